@@ -1,0 +1,151 @@
+"""CPU: pins both oracles (oracle/ref_scan.py, oracle/cudasp_oracle.c) to the golden vectors
+generated from the reference's own Python (tests/golden/make_golden.py)."""
+import numpy as np
+import pytest
+
+from oracle import c_oracle as CO
+from oracle import ref_scan as R
+
+
+def I(hexstr):
+    return int(hexstr, 16)
+
+
+def pt_blob(xy):
+    return R.encode_point((I(xy[0]), I(xy[1])))
+
+
+def test_field_kats_c(golden):
+    for k in golden["field"]:
+        a, b = I(k["a"]), I(k["b"])
+        assert CO.fe_op(0, a, b) == I(k["mul"])
+        assert CO.fe_op(1, a, b) == I(k["add"])
+        assert CO.fe_op(2, a, b) == I(k["sub"])
+        if a:
+            assert CO.fe_op(3, a) == I(k["inv"])
+
+
+@pytest.mark.parametrize("key", ["pmul_seed42", "pmul_gpu_dumps", "pmul_batch_seed42"])
+def test_pmul_kats(golden, key):
+    for i, k in enumerate(golden[key]):
+        blob = pt_blob([k["x"], k["y"]])
+        out, inf = CO.pt_mul(I(k["s"]).to_bytes(32, "little"), blob)
+        assert not inf and R.parse_point(out) == (I(k["rx"]), I(k["ry"]))
+        if i < 4:
+            assert R.pt_mul(I(k["s"]), R.parse_point(blob)) == (I(k["rx"]), I(k["ry"]))
+
+
+def test_g_multiples(golden):
+    g = R.encode_point(R.G)
+    for k in golden["g_multiples"]:
+        out, inf = CO.pt_mul(I(k["k"]).to_bytes(32, "little"), g)
+        assert R.parse_point(out) == (I(k["rx"]), I(k["ry"]))
+        assert R.pt_mul(I(k["k"]), R.G) == (I(k["rx"]), I(k["ry"]))
+
+
+def test_tagged_hash(golden):
+    for k in golden["tagged_hash"]:
+        msg = bytes.fromhex(k["msg"])
+        assert R.tagged_hash(msg).hex() == k["hash"]
+        assert CO.tagged_hash(msg).hex() == k["hash"]
+
+
+def test_upper64(golden):
+    for hx, want in golden["upper64_cases"]:
+        assert R.upper64_signed(I(hx) << 192) == want
+
+
+def test_pipeline_kats(golden):
+    for i, k in enumerate(golden["pipeline"]):
+        sk = I(k["sk"]).to_bytes(32, "little")
+        labels = [pt_blob(l) for l in k["labels"]]
+        r = CO.row(sk, pt_blob(k["spend"]), labels, pt_blob(k["tweak"]))
+        assert r["cands"] == k["cands"]
+        assert r["S"] == (I(k["S"][0]), I(k["S"][1]))
+        assert r["t"] == I(k["t"])
+        assert r["P0"] == (I(k["P0"][0]), I(k["P0"][1]))
+        if i < 6:
+            p = R.row_intermediates(I(k["sk"]), R.parse_point(pt_blob(k["tweak"])), R.parse_point(pt_blob(k["spend"])),
+                                    [R.parse_point(b) for b in labels])
+            assert p["cands"] == k["cands"] and p["msg"].hex() == k["msg"] and p["t"] == I(k["t"])
+            assert p["T"] == (I(k["T"][0]), I(k["T"][1]))
+
+
+def test_bip352_vector(golden):
+    b = golden["bip352_vector"]
+    sk = bytes.fromhex(b["scan_sk_be"])[::-1]
+    spend, tweak = bytes.fromhex(b["spend_le"]), bytes.fromhex(b["tweak_le"])
+    p = R.row_intermediates(R.parse_scalar(sk), R.parse_point(tweak), R.parse_point(spend))
+    assert format(p["S"][0], "064x") == b["S_x"] and format(p["S"][1], "064x") == b["S_y"]
+    assert p["msg"].hex() == b["msg"] and format(p["t"], "064x") == b["t"]
+    assert format(p["T"][0], "064x") == b["T_x"] and format(p["P0"][0], "064x") == b["P0_x"]
+    assert p["cands"] == [b["expected"]] and int(b["upper64"]) == b["expected"]
+    assert CO.row(sk, spend, [], tweak)["cands"] == [b["expected"]]
+
+
+def _sql_rows(golden, q):
+    rows = golden["sql"]["test_data"][: q["rows_visible"]]
+    if q["where_height"] is not None:
+        rows = [r for r in rows if r["height"] == q["where_height"]]
+    return rows
+
+
+def test_sql_cases_both_oracles(golden):
+    """Every query of test/sql/cudasp.test on test_data (the replicated tables are covered in
+    test_sql_replicated)."""
+    for q in golden["sql"]["queries"]:
+        if q["table"] != "test_data":
+            continue
+        rows = _sql_rows(golden, q)
+        sk, spend = bytes.fromhex(q["scan_sk"]), bytes.fromhex(q["spend"])
+        labels = [bytes.fromhex(l) for l in q["labels"]]
+        got = R.scan_rows(sk, spend, labels, [(bytes.fromhex(r["txid"]), r["height"], bytes.fromhex(r["tweak"]), r["outputs"]) for r in rows])
+        tw = np.frombuffer(b"".join(bytes.fromhex(r["tweak"]) for r in rows), np.uint8).reshape(-1, 64)
+        outs = np.array([o for r in rows for o in r["outputs"]], np.int64)
+        off = np.cumsum([0] + [len(r["outputs"]) for r in rows]).astype(np.uint32)
+        flags, _ = CO.scan(sk, spend, labels, tw, outs, off)
+        heights_c = [r["height"] for r, f in zip(rows, flags) if f]
+        if q["select"] == "COUNT(*)":
+            assert len(got) == q["expect"] and len(heights_c) == q["expect"]
+        else:
+            assert [g[1] for g in got] == [q["expect"]] and heights_c == [q["expect"]]
+
+
+def test_sql_replicated(golden):
+    rep = golden["sql"]["replicated"]
+    q = [q for q in golden["sql"]["queries"] if q["table"] == "large_test"][0]
+    n = 257  # the 20 K / 200 K tables are this one row replicated; full size runs on the GPU
+    tw = np.frombuffer(bytes.fromhex(rep["tweak"]) * n, np.uint8).reshape(-1, 64)
+    outs = np.array(rep["outputs"] * n, np.int64)
+    off = (np.arange(n + 1) * len(rep["outputs"])).astype(np.uint32)
+    flags, _ = CO.scan(bytes.fromhex(q["scan_sk"]), bytes.fromhex(q["spend"]), [], tw, outs, off, threads=2)
+    assert int(flags.sum()) == n
+
+
+def test_h400_base_candidate_is_not_label_candidate(golden):
+    """h=400 base candidate is -1006811617310360495, label candidate -1265772155233867786."""
+    q = [q for q in golden["sql"]["queries"] if q["where_height"] == 400 and q["labels"]][0]
+    row = [r for r in golden["sql"]["test_data"] if r["height"] == 400][0]
+    r = CO.row(bytes.fromhex(q["scan_sk"]), bytes.fromhex(q["spend"]), [bytes.fromhex(l) for l in q["labels"]], bytes.fromhex(row["tweak"]))
+    assert r["cands"] == [-1006811617310360495, -1265772155233867786]
+
+
+def test_edge_semantics():
+    # NULL / empty outputs never match; NULL children skipped; NULL key columns dropped
+    assert not R.row_matches([5], None) and not R.row_matches([5], []) and not R.row_matches([5], [None])
+    assert R.row_matches([5, 7], [None, 7])
+    sk, spend = R.encode_scalar(12345), R.encode_point(R.G)
+    tw = R.encode_point(R.pt_mul(99, R.G))
+    c = R.row_candidates(12345, R.parse_point(tw), R.G)[0]
+    rows = [(b"a", 1, tw, [c]), (None, 1, tw, [c]), (b"b", None, tw, [c]), (b"c", 1, None, [c]), (b"d", 2, tw, None), (b"e", 3, tw, [c ^ 1])]
+    assert R.scan_rows(sk, spend, [], rows) == [(b"a", 1, tw)]
+    # infinity -> x = 1 -> candidate 0: label = -(P0)
+    P0 = R.row_intermediates(12345, R.parse_point(tw), R.G)["P0"]
+    neg = (P0[0], R.P - P0[1])
+    assert R.row_candidates(12345, R.parse_point(tw), R.G, [neg, P0]) == [c, 0, R.upper64_signed(R.pt_double(P0)[0])]
+    r = CO.row(sk, spend, [R.encode_point(neg), R.encode_point(P0)], tw)
+    assert r["cands"] == [c, 0, R.upper64_signed(R.pt_double(P0)[0])]
+    # scalar zero: shared secret is the all-zero coordinate pair in the reference
+    z = R.row_intermediates(0, R.parse_point(tw), R.G)
+    assert z["msg"] == b"\x02" + b"\x00" * 36
+    assert CO.row(R.encode_scalar(0), spend, [], tw)["cands"] == z["cands"]
