@@ -1,0 +1,408 @@
+// cudasp_capi.cu -- implementation of include/cudasp.h (the drop-in C ABI).
+//
+// Replaces LaunchBatchScan / RunBatchScanKernels / FreeBatchScanState and their BatchScanState
+// (src/cudasp_gpu.cu:425-1023): where the reference allocates ~20 buffers, creates a stream and
+// synchronises >= 5 times per batch, this layer allocates everything once per query, keeps
+// SLOTS_PER_DEVICE pinned+device staging slots per GPU, each with its own stream, and runs a batch
+// as: 3 async H2D copies -> 5 (L = 0) or 7 (L > 0) kernels -> one small async D2H (count + first ids).
+// No host synchronisation happens until the caller asks for a result.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/cudasp.h"
+#include "kernels.cuh"
+#include "query_plan.hpp"
+
+using namespace csp;
+
+namespace {
+
+thread_local std::string tl_err;
+
+const int SLOTS_PER_DEVICE = 3;
+const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
+const int LADDER_BLOCK = 128, LADDER_MINB = 3;
+const int HASH_BLOCK = 128, HASH_MINB = 3;
+const int FINAL_BLOCK = 128;
+const uint32_t INV_ROWS_PER_THREAD = 16;
+
+struct Workspace {          // device-only scratch for one batch in flight
+  fe *X = nullptr, *Y = nullptr, *Z = nullptr, *S = nullptr;   // rows each
+  fe *D = nullptr, *DS = nullptr;                              // L * rows each (labels only)
+  uint8_t *flags = nullptr;
+  cudaEvent_t free_evt = nullptr;                              // recorded after the last kernel using it
+  uint32_t cap_rows = 0;
+};
+
+struct Slot {
+  uint32_t id = 0;
+  int dev_index = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;
+  // pinned host staging
+  uint8_t *h_tweaks = nullptr;
+  int64_t *h_outputs = nullptr;
+  uint32_t *h_off = nullptr;
+  uint32_t *h_result = nullptr;   // [0] = count, [1 ..] = ids (cap_rows)
+  // device inputs / outputs
+  uint8_t *d_tweaks = nullptr;
+  int64_t *d_outputs = nullptr;
+  uint32_t *d_off = nullptr;
+  uint32_t *d_result = nullptr;   // [0] = count, [1 ..] = ids
+  uint32_t cap_rows = 0;
+  uint64_t cap_outputs = 0;
+  Workspace ws;
+  // state
+  int state = 0;                  // 0 free, 1 acquired, 2 in flight, 3 result handed out
+  uint64_t tag = 0;
+  uint32_t rows = 0;
+  bool internal = false;          // owned by a synchronous call (not visible to poll/wait)
+};
+
+struct DevCtx {
+  int device = 0;
+  ge *d_gtab = nullptr;
+  ge *d_labels = nullptr;
+  cudaStream_t own_stream = nullptr;
+  std::vector<Slot *> slots;
+  uint32_t next_ws = 0;
+};
+
+}  // namespace
+
+struct cudasp_query {
+  host::QueryPlan plan;
+  uint32_t n_labels = 0;
+  uint32_t batch_rows = 0;
+  std::vector<DevCtx> devs;
+  std::vector<Slot *> all_slots;
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<Slot *> inflight;   // public streaming API, submit order
+  uint32_t rr = 0;               // round-robin cursor for slot acquisition
+  std::string err;
+  std::atomic<uint64_t> launches{0};
+};
+
+namespace {
+
+int fail(cudasp_query *q, int code, const std::string &msg) {
+  tl_err = msg;
+  if (q) {
+    std::lock_guard<std::mutex> lk(q->mu);
+    q->err = msg;
+  }
+  return code;
+}
+#define CU(q, call)                                                                                      \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess)                                                                               \
+      return fail(q, CUDASP_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));               \
+  } while (0)
+
+// ---- per-process, per-device fixed-base table
+std::mutex g_gtab_mu;
+std::vector<ge *> g_gtab_dev;   // indexed by device ordinal
+
+int get_device_gtab(cudasp_query *q, int device, ge **out) {
+  std::lock_guard<std::mutex> lk(g_gtab_mu);
+  if ((int)g_gtab_dev.size() <= device) g_gtab_dev.resize(device + 1, nullptr);
+  if (!g_gtab_dev[device]) {
+    const host::GTabHost &g = host::gtab_host();
+    ge *d = nullptr;
+    CU(q, cudaSetDevice(device));
+    CU(q, cudaMalloc(&d, g.table.size() * sizeof(ge)));
+    CU(q, cudaMemcpy(d, g.table.data(), g.table.size() * sizeof(ge), cudaMemcpyHostToDevice));
+    g_gtab_dev[device] = d;
+  }
+  *out = g_gtab_dev[device];
+  return 0;
+}
+
+int alloc_workspace(cudasp_query *q, Workspace &w, uint32_t rows, uint32_t L) {
+  w.cap_rows = rows;
+  size_t n = (size_t)rows;
+  CU(q, cudaMalloc(&w.X, n * sizeof(fe)));
+  CU(q, cudaMalloc(&w.Y, n * sizeof(fe)));
+  CU(q, cudaMalloc(&w.Z, n * sizeof(fe)));
+  CU(q, cudaMalloc(&w.S, n * sizeof(fe)));
+  if (L) {
+    CU(q, cudaMalloc(&w.D, n * L * sizeof(fe)));
+    CU(q, cudaMalloc(&w.DS, n * L * sizeof(fe)));
+    CU(q, cudaMalloc(&w.flags, n));
+  }
+  CU(q, cudaEventCreateWithFlags(&w.free_evt, cudaEventDisableTiming));
+  return 0;
+}
+void free_workspace(Workspace &w) {
+  cudaFree(w.X); cudaFree(w.Y); cudaFree(w.Z); cudaFree(w.S); cudaFree(w.D); cudaFree(w.DS); cudaFree(w.flags);
+  if (w.free_evt) cudaEventDestroy(w.free_evt);
+  w = Workspace();
+}
+
+int alloc_slot_outputs(cudasp_query *q, Slot &s, uint64_t cap_outputs) {
+  if (s.h_outputs) cudaFreeHost(s.h_outputs);
+  if (s.d_outputs) cudaFree(s.d_outputs);
+  s.h_outputs = nullptr; s.d_outputs = nullptr;
+  s.cap_outputs = cap_outputs;
+  CU(q, cudaHostAlloc((void **)&s.h_outputs, std::max<uint64_t>(cap_outputs, 1) * sizeof(int64_t), cudaHostAllocDefault));
+  CU(q, cudaMalloc(&s.d_outputs, std::max<uint64_t>(cap_outputs, 1) * sizeof(int64_t)));
+  return 0;
+}
+
+int alloc_slot(cudasp_query *q, Slot &s, int device, uint32_t rows, uint64_t cap_outputs, uint32_t L) {
+  CU(q, cudaSetDevice(device));
+  s.cap_rows = rows;
+  CU(q, cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+  CU(q, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  CU(q, cudaHostAlloc((void **)&s.h_tweaks, (size_t)rows * 64, cudaHostAllocDefault));
+  CU(q, cudaHostAlloc((void **)&s.h_off, ((size_t)rows + 1) * 4, cudaHostAllocDefault));
+  CU(q, cudaHostAlloc((void **)&s.h_result, ((size_t)rows + 1) * 4, cudaHostAllocDefault));
+  CU(q, cudaMalloc(&s.d_tweaks, (size_t)rows * 64));
+  CU(q, cudaMalloc(&s.d_off, ((size_t)rows + 1) * 4));
+  CU(q, cudaMalloc(&s.d_result, ((size_t)rows + 1) * 4));
+  int rc = alloc_slot_outputs(q, s, cap_outputs);
+  if (rc) return rc;
+  return alloc_workspace(q, s.ws, rows, L);
+}
+void free_slot(Slot &s) {
+  cudaFreeHost(s.h_tweaks); cudaFreeHost(s.h_outputs); cudaFreeHost(s.h_off); cudaFreeHost(s.h_result);
+  cudaFree(s.d_tweaks); cudaFree(s.d_outputs); cudaFree(s.d_off); cudaFree(s.d_result);
+  free_workspace(s.ws);
+  if (s.done) cudaEventDestroy(s.done);
+  if (s.stream) cudaStreamDestroy(s.stream);
+}
+
+uint32_t inv_threads(uint32_t n) {
+  uint32_t t = (n + INV_ROWS_PER_THREAD - 1) / INV_ROWS_PER_THREAD;
+  t = (t + 127u) / 128u * 128u;
+  return std::max<uint32_t>(std::min<uint32_t>(t, n), 1u);
+}
+
+// Enqueue the whole per-batch pipeline on `st`.  All pointers are device pointers.
+// d_result: [0] = match count (reset here), [1..] = ids.  Either may be NULL (candidate mode).
+int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_tweaks, const int64_t *d_outputs,
+                    const uint32_t *d_off, uint32_t rows, uint32_t *d_ids, uint32_t *d_count, cudaStream_t st,
+                    int64_t *d_cands, uint8_t *dbg_S, uint8_t *dbg_t, uint8_t *dbg_P0) {
+  if (rows == 0) {
+    if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
+    return 0;
+  }
+  if (rows > w.cap_rows) return fail(q, CUDASP_ERR_ARG, "rows exceed the workspace capacity");
+  const uint32_t L = q->n_labels;
+  const host::QueryPlan &pl = q->plan;
+  uint64_t nl = 0;
+  if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
+  if (!pl.fp.zero_scalar) {
+    const uint32_t grid = (rows + LADDER_BLOCK - 1) / LADDER_BLOCK;
+    k_ladder<LADDER_BLOCK, LADDER_MINB><<<grid, LADDER_BLOCK, LADDER_SMEM_WORDS_PER_THREAD * 4 * LADDER_BLOCK, st>>>(
+        d_tweaks, w.X, w.Y, w.Z, rows, pl.lp);
+    const uint32_t T = inv_threads(rows);
+    k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
+    nl += 2;
+  }
+  {
+    const uint32_t grid = (rows + HASH_BLOCK - 1) / HASH_BLOCK;
+    k_hash_fixedbase<HASH_BLOCK, HASH_MINB><<<grid, HASH_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, dc.d_gtab, pl.fp, dbg_S, dbg_t);
+    const uint32_t T = inv_threads(rows);
+    k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
+    const uint32_t fgrid = (rows + FINAL_BLOCK - 1) / FINAL_BLOCK;
+    k_final_base<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, d_outputs, d_off, dc.d_labels, L, w.D, w.flags,
+                                                            d_ids, d_count, d_cands, dbg_P0);
+    nl += 3;
+    if (L) {
+      const uint64_t n64 = (uint64_t)rows * L;
+      if (n64 > 0xffffffffull) return fail(q, CUDASP_ERR_ARG, "rows * labels exceeds 2^32");
+      const uint32_t n = (uint32_t)n64, T2 = inv_threads(n);
+      k_batch_inv<<<(T2 + 127) / 128, 128, 0, st>>>(w.D, w.DS, n, T2);
+      k_final_labels<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.D, rows, d_outputs, d_off, dc.d_labels, L, w.flags,
+                                                                d_ids, d_count, d_cands);
+      nl += 2;
+    }
+  }
+  CU(q, cudaGetLastError());
+  q->launches += nl;
+  return 0;
+}
+
+}  // namespace
+
+// =====================================================================================
+extern "C" {
+
+const char *cudasp_version(void) { return "cudasp-b200 0.1 (sm_100a)"; }
+
+int cudasp_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+const char *cudasp_last_error(const cudasp_query *q) {
+  if (q) return q->err.c_str();
+  return tl_err.c_str();
+}
+
+void cudasp_query_destroy(cudasp_query *q) {
+  if (!q) return;
+  for (DevCtx &dc : q->devs) {
+    cudaSetDevice(dc.device);
+    cudaDeviceSynchronize();
+    for (Slot *s : dc.slots) { free_slot(*s); delete s; }
+    cudaFree(dc.d_labels);
+    if (dc.own_stream) cudaStreamDestroy(dc.own_stream);
+  }
+  delete q;
+}
+
+int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64], const uint8_t *label_keys,
+                        uint32_t n_labels, const int *devices, int n_devices, uint32_t batch_rows,
+                        uint64_t max_outputs_per_batch, cudasp_query **out) {
+  if (!out) return fail(nullptr, CUDASP_ERR_ARG, "out is NULL");
+  *out = nullptr;
+  if (!scan_private_key || !spend_public_key) return fail(nullptr, CUDASP_ERR_ARG, "key pointer is NULL");
+  if (n_labels > CUDASP_MAX_LABELS) return fail(nullptr, CUDASP_ERR_ARG, "too many label keys");
+  if (n_labels && !label_keys) return fail(nullptr, CUDASP_ERR_ARG, "label_keys is NULL");
+  if (batch_rows == 0 || batch_rows > CUDASP_MAX_BATCH_ROWS) return fail(nullptr, CUDASP_ERR_ARG, "batch_rows out of range");
+  const int visible = cudasp_device_count();
+  if (visible <= 0) return fail(nullptr, CUDASP_ERR_CUDA, "no CUDA device available (this library has no CPU path)");
+  std::vector<int> devs;
+  if (n_devices <= 0) n_devices = devices ? 0 : visible;
+  for (int i = 0; i < n_devices; i++) {
+    int d = devices ? devices[i] : i;
+    if (d < 0 || d >= visible) return fail(nullptr, CUDASP_ERR_ARG, "device ordinal out of range");
+    devs.push_back(d);
+  }
+  if (devs.empty()) return fail(nullptr, CUDASP_ERR_ARG, "empty device list");
+
+  cudasp_query *q = new cudasp_query();
+  std::string err;
+  int rc = host::make_query_plan(q->plan, scan_private_key, spend_public_key, label_keys, n_labels, err);
+  if (rc) { delete q; return fail(nullptr, rc == -4 ? CUDASP_ERR_KEY : CUDASP_ERR_ARG, err); }
+  q->n_labels = n_labels;
+  q->batch_rows = batch_rows;
+  if (max_outputs_per_batch == 0) max_outputs_per_batch = 8ull * batch_rows;
+  q->devs.resize(devs.size());
+  uint32_t slot_id = 0;
+  for (size_t i = 0; i < devs.size(); i++) {
+    DevCtx &dc = q->devs[i];
+    dc.device = devs[i];
+    rc = get_device_gtab(nullptr, dc.device, &dc.d_gtab);
+    if (rc) { cudasp_query_destroy(q); return rc; }
+    cudaError_t e = cudaSetDevice(dc.device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&dc.own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess && n_labels) {
+      e = cudaMalloc(&dc.d_labels, n_labels * sizeof(ge));
+      if (e == cudaSuccess) e = cudaMemcpy(dc.d_labels, q->plan.labels.data(), n_labels * sizeof(ge), cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) { cudasp_query_destroy(q); return fail(nullptr, CUDASP_ERR_CUDA, cudaGetErrorString(e)); }
+    for (int k = 0; k < SLOTS_PER_DEVICE; k++) {
+      Slot *s = new Slot();
+      s->id = slot_id++;
+      s->dev_index = (int)i;
+      dc.slots.push_back(s);
+      q->all_slots.push_back(s);
+      rc = alloc_slot(nullptr, *s, dc.device, batch_rows, max_outputs_per_batch, n_labels);
+      if (rc) { std::string m = tl_err; cudasp_query_destroy(q); return fail(nullptr, rc, m); }
+    }
+  }
+  *out = q;
+  return CUDASP_OK;
+}
+
+uint64_t cudasp_launch_count(const cudasp_query *q) { return q ? q->launches.load() : 0; }
+
+int cudasp_query_info(const cudasp_query *q, int *n_devices, int *ladder_dbl, int *ladder_add, int *fixed_window_bits,
+                      int *n_labels) {
+  if (!q) return CUDASP_ERR_ARG;
+  if (n_devices) *n_devices = (int)q->devs.size();
+  if (ladder_dbl) *ladder_dbl = q->plan.n_dbl;
+  if (ladder_add) *ladder_add = q->plan.n_add;
+  if (fixed_window_bits) *fixed_window_bits = GTAB_WBITS;
+  if (n_labels) *n_labels = (int)q->n_labels;
+  return CUDASP_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// ---- slot pool ------------------------------------------------------------------------
+Slot *try_acquire_locked(cudasp_query *q) {
+  const size_t n = q->all_slots.size();
+  // interleave devices: slot ids are device-major, so walk with a stride of SLOTS_PER_DEVICE
+  for (size_t k = 0; k < n; k++) {
+    size_t idx = (q->rr + k) % n;
+    size_t dev = idx % q->devs.size(), j = idx / q->devs.size();
+    Slot *s = q->devs[dev].slots[j];
+    if (s->state == 0) {
+      s->state = 1;
+      q->rr = (uint32_t)((idx + 1) % n);
+      return s;
+    }
+  }
+  return nullptr;
+}
+Slot *acquire_blocking(cudasp_query *q) {
+  std::unique_lock<std::mutex> lk(q->mu);
+  Slot *s;
+  while (!(s = try_acquire_locked(q))) q->cv.wait(lk);
+  return s;
+}
+void release_slot(cudasp_query *q, Slot *s) {
+  {
+    std::lock_guard<std::mutex> lk(q->mu);
+    s->state = 0;
+    s->internal = false;
+  }
+  q->cv.notify_all();
+}
+
+int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t tag) {
+  DevCtx &dc = q->devs[s->dev_index];
+  CU(q, cudaSetDevice(dc.device));
+  cudaStream_t st = s->stream;
+  s->rows = rows;
+  s->tag = tag;
+  if (rows) {
+    CU(q, cudaMemcpyAsync(s->d_tweaks, s->h_tweaks, (size_t)rows * 64, cudaMemcpyHostToDevice, st));
+    CU(q, cudaMemcpyAsync(s->d_off, s->h_off, ((size_t)rows + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (n_outputs) CU(q, cudaMemcpyAsync(s->d_outputs, s->h_outputs, n_outputs * 8, cudaMemcpyHostToDevice, st));
+  }
+  CU(q, cudaStreamWaitEvent(st, s->ws.free_evt, 0));
+  int rc = launch_pipeline(q, dc, s->ws, s->d_tweaks, s->d_outputs, s->d_off, rows, s->d_result + 1, s->d_result, st,
+                           nullptr, nullptr, nullptr, nullptr);
+  if (rc) return rc;
+  CU(q, cudaEventRecord(s->ws.free_evt, st));
+  const uint32_t eager = std::min<uint32_t>(rows, EAGER_IDS);
+  CU(q, cudaMemcpyAsync(s->h_result, s->d_result, ((size_t)eager + 1) * 4, cudaMemcpyDeviceToHost, st));
+  CU(q, cudaEventRecord(s->done, st));
+  return 0;
+}
+
+// wait for the slot's batch, bring back all ids, sort them ascending
+int finish(cudasp_query *q, Slot *s, uint32_t *n_matches) {
+  DevCtx &dc = q->devs[s->dev_index];
+  CU(q, cudaSetDevice(dc.device));
+  CU(q, cudaEventSynchronize(s->done));
+  uint32_t n = s->h_result[0];
+  if (n > s->rows) return fail(q, CUDASP_ERR_STATE, "internal: match count exceeds rows");
+  if (n > EAGER_IDS) {
+    CU(q, cudaMemcpyAsync(s->h_result + 1 + EAGER_IDS, s->d_result + 1 + EAGER_IDS, ((size_t)n - EAGER_IDS) * 4,
+                          cudaMemcpyDeviceToHost, s->stream));
+    CU(q, cudaStreamSynchronize(s->stream));
+  }
+  std::sort(s->h_result + 1, s->h_result + 1 + n);
+  *n_matches = n;
+  return 0;
+}
+
+}  // namespace

@@ -1,0 +1,105 @@
+// query_plan.hpp -- everything that is computed once per query (host side), shared by the C ABI
+// (cudasp_capi.cu) and by the CPU-side logic tests (tests/hostcheck).
+//
+// Reference counterpart: the key conversions repeated per batch in ProcessBatch
+// (src/cudasp_extension.cu:277-297,343-361) and per thread in CheckMatchesWithLabelsKernel
+// (spend key / labels to Montgomery form, src/cudasp_gpu.cu:109-116,154-161).
+#pragma once
+#include <mutex>
+#include <string>
+#include <vector>
+#include "host_ec.hpp"
+#include "rowfn.cuh"
+
+namespace csp {
+namespace host {
+
+struct GTabHost {
+  std::vector<ge> table;   // [GTAB_NWIN][GTAB_ENTRIES]
+  Big offset_sum;          // sum of r_w mod n
+  HPoint offset_point;     // offset_sum * G
+};
+inline const GTabHost &gtab_host() {
+  static GTabHost g;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    build_gtab(g.table, g.offset_sum, GTAB_WBITS, GTAB_NWIN);
+    g.offset_point = h_mul(g.offset_sum, generator());
+  });
+  return g;
+}
+
+struct QueryPlan {
+  LadderParams lp;
+  FinalParams fp;
+  std::vector<ge> labels;
+  int n_dbl, n_add;
+};
+
+inline bool point_from_blob(HPoint &p, const uint8_t b[64]) {
+  fe_from_le_bytes(p.x, b);
+  fe_from_le_bytes(p.y, b + 32);
+  p.inf = false;
+  return true;
+}
+
+// Checks that the op list never adds a point to itself or its negative: simulate the scalar
+// (a + b*lambda mod n) the accumulator holds before every ADD.
+inline bool ladder_plan_is_regular(const LadderPlan &p) {
+  const Big n = N_ORDER(), lam = LAMBDA();
+  Big v;  // accumulator scalar mod n
+  for (int i = 0; i < p.nops; i++) {
+    uint8_t op = p.ops[i];
+    if (op & OP_DBL) { v = mod(shl1(v), n); continue; }
+    Big d((uint64_t)(2 * (op & 3) + 1));
+    if (op & OP_LAMBDA) d = mod(mul(d, lam), n);
+    if (op & OP_NEG) d = sub(n, d);
+    if (!(op & OP_SET)) {
+      if (cmp(v, d) == 0) return false;
+      if (cmp(mod(add(v, d), n), Big()) == 0) return false;
+      if (v.is_zero()) return false;
+    }
+    v = mod(add(v, d), n);
+  }
+  return !v.is_zero();
+}
+
+// returns 0, or a negative CUDASP_ERR_* with err set
+inline int make_query_plan(QueryPlan &q, const uint8_t sk[32], const uint8_t spend[64], const uint8_t *labels,
+                           uint32_t n_labels, std::string &err) {
+  memset(&q.lp, 0, sizeof q.lp);
+  memset(&q.fp, 0, sizeof q.fp);
+  LadderPlan lp = make_ladder_plan(sk);
+  q.n_dbl = lp.n_dbl;
+  q.n_add = lp.n_add;
+  if (!lp.zero) {
+    if (lp.nops > LADDER_MAX_OPS_DEV) { err = "internal: ladder op list too long"; return -4; }
+    if (!ladder_plan_is_regular(lp)) { err = "scan_private_key yields a degenerate ladder schedule"; return -4; }
+    // the schedule must reproduce k: checked by ladder_plan_is_regular's final scalar in tests
+    memcpy(q.lp.ops, lp.ops, (size_t)lp.nops);
+    q.lp.nops = lp.nops;
+  }
+  for (int i = 0; i < 8; i++) q.lp.beta[i] = BETA_LIMBS[i];
+  q.fp.zero_scalar = lp.zero ? 1 : 0;
+  bip352_midstate(q.fp.midstate);
+  // spend_adj = B_spend - offset_point
+  HPoint B;
+  point_from_blob(B, spend);
+  const GTabHost &g = gtab_host();
+  HPoint adj = h_add(B, h_neg(g.offset_point));
+  q.fp.spend_adj_inf = adj.inf ? 1 : 0;
+  q.fp.spend_adj_x = adj.x;
+  q.fp.spend_adj_y = adj.y;
+  q.labels.resize(n_labels);
+  for (uint32_t i = 0; i < n_labels; i++) {
+    fe_from_le_bytes(q.labels[i].x, labels + 64 * (size_t)i);
+    fe_from_le_bytes(q.labels[i].y, labels + 64 * (size_t)i + 32);
+    // labels >= p are legal blobs; canonicalise once so that xL - x0 == 0 is an exact test
+    fe_normalize(q.labels[i].x);
+    fe_normalize(q.labels[i].y);
+  }
+  return 0;
+}
+
+}  // namespace host
+}  // namespace csp

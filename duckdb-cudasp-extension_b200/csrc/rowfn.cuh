@@ -1,0 +1,281 @@
+// rowfn.cuh -- the per-row stages of the scan as __host__ __device__ functions.
+//
+// The kernels in kernels.cuh are thin wrappers (thread <-> row mapping, memory layout, match
+// compaction) around these functions; tests/hostcheck compiles the very same functions with g++
+// so that the schedule logic (GLV/wNAF op list, isomorphic odd-multiples table, offset fixed-base
+// windows, chord/tangent label rule, batch inversion) is verified on the CPU against the oracle
+// before any GPU time is spent.  That host build is test infrastructure only: the C ABI never
+// calls it and has no CPU path.
+#pragma once
+#include <stdint.h>
+#include "fe.cuh"
+#include "ge.cuh"
+#include "sha256.cuh"
+
+namespace csp {
+
+static const int LADDER_MAX_OPS_DEV = 240;
+static const int GTAB_WBITS = 8;                       // fixed-base window width
+static const int GTAB_NWIN = 256 / GTAB_WBITS;         // 32 windows
+static const int GTAB_ENTRIES = 1 << GTAB_WBITS;
+
+struct LadderParams {          // kernel parameter (constant bank): the per-query op list
+  uint8_t ops[LADDER_MAX_OPS_DEV];
+  int32_t nops;
+  uint32_t beta[8];
+};
+
+struct FinalParams {           // kernel parameter: per-query constants of K3
+  uint32_t midstate[8];        // SHA-256 chaining value after TH||TH
+  fe spend_adj_x, spend_adj_y; // B_spend minus the fixed-base table's offset point
+  int32_t spend_adj_inf;       // that difference is the point at infinity: skip the add
+  int32_t zero_scalar;         // scan key = 0 (mod n): S is the reference's all-zero pair
+};
+
+// ---------------------------------------------------------------- row <-> memory
+CSP_HD void load_fe(fe &r, const fe *p) {
+#if defined(__CUDA_ARCH__)
+  const uint4 *q = reinterpret_cast<const uint4 *>(p);
+  uint4 a = q[0], b = q[1];
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+#else
+  r = *p;
+#endif
+}
+CSP_HD void load_fe_ro(fe &r, const fe *p) {   // read-only path (tables, inputs)
+#if defined(__CUDA_ARCH__)
+  const uint4 *q = reinterpret_cast<const uint4 *>(p);
+  uint4 a = __ldg(q), b = __ldg(q + 1);
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+#else
+  r = *p;
+#endif
+}
+CSP_HD void store_fe(fe *p, const fe &r) {
+#if defined(__CUDA_ARCH__)
+  uint4 *q = reinterpret_cast<uint4 *>(p);
+  q[0] = make_uint4(r.v[0], r.v[1], r.v[2], r.v[3]);
+  q[1] = make_uint4(r.v[4], r.v[5], r.v[6], r.v[7]);
+#else
+  *p = r;
+#endif
+}
+
+// ---------------------------------------------------------------- K1 body: S = scan_sk * P
+// Tab: storage for the 4-entry odd-multiples table, components 0 = x, 1 = beta*x, 2 = y;
+//      needs  uint32_t get(e, c, l)  and  void set(e, c, l, v).
+// Result: Jacobian S (not normalised to Z = 1; the caller batches the inversion).
+template <class Tab>
+CSP_HD void ladder_row(gej &acc, const ge &P, const LadderParams &prm, Tab &tab) {
+  // d = 2P (Jacobian).  Work on the curve isomorphic by dz, where d is affine.
+  gej d;
+  {
+    gej pj;
+    pj.x = P.x; pj.y = P.y; fe_set_u32(pj.z, 1);
+    gej_dbl(d, pj);
+  }
+  fe dz2, dz3;
+  fe_sqr(dz2, d.z);
+  fe_mul(dz3, dz2, d.z);
+  gej e[4];
+  fe h1, h2, h3;
+  fe_mul(e[0].x, P.x, dz2);
+  fe_mul(e[0].y, P.y, dz3);
+  fe_set_u32(e[0].z, 1);
+  gej_add_ge(e[1], e[0], d.x, d.y, &h1);   // 3P'
+  gej_add_ge(e[2], e[1], d.x, d.y, &h2);   // 5P'
+  gej_add_ge(e[3], e[2], d.x, d.y, &h3);   // 7P'
+  // bring all four to the common Z = e[3].z:  scale entry i by s_i = Z3/Z_i
+  //   s_2 = h3, s_1 = h2*h3, s_0 = h1*h2*h3 = Z3
+  fe beta;
+#pragma unroll
+  for (int l = 0; l < 8; l++) beta.v[l] = prm.beta[l];
+  {
+    fe s, s2, s3, x, y, bx;
+    // entry 3: as is
+    fe_mul(bx, e[3].x, beta);
+#pragma unroll
+    for (int l = 0; l < 8; l++) { tab.set(3, 0, l, e[3].x.v[l]); tab.set(3, 1, l, bx.v[l]); tab.set(3, 2, l, e[3].y.v[l]); }
+    // entry 2: s = h3
+    s = h3;
+    fe_sqr(s2, s); fe_mul(s3, s2, s);
+    fe_mul(x, e[2].x, s2); fe_mul(y, e[2].y, s3); fe_mul(bx, x, beta);
+#pragma unroll
+    for (int l = 0; l < 8; l++) { tab.set(2, 0, l, x.v[l]); tab.set(2, 1, l, bx.v[l]); tab.set(2, 2, l, y.v[l]); }
+    // entry 1: s = h2*h3
+    fe_mul(s, h2, h3);
+    fe_sqr(s2, s); fe_mul(s3, s2, s);
+    fe_mul(x, e[1].x, s2); fe_mul(y, e[1].y, s3); fe_mul(bx, x, beta);
+#pragma unroll
+    for (int l = 0; l < 8; l++) { tab.set(1, 0, l, x.v[l]); tab.set(1, 1, l, bx.v[l]); tab.set(1, 2, l, y.v[l]); }
+    // entry 0: s = Z3 (e[0].z = 1)
+    s = e[3].z;
+    fe_sqr(s2, s); fe_mul(s3, s2, s);
+    fe_mul(x, e[0].x, s2); fe_mul(y, e[0].y, s3); fe_mul(bx, x, beta);
+#pragma unroll
+    for (int l = 0; l < 8; l++) { tab.set(0, 0, l, x.v[l]); tab.set(0, 1, l, bx.v[l]); tab.set(0, 2, l, y.v[l]); }
+  }
+  // Z of the final result must be multiplied by zscale = Z3 * dz
+  fe zscale;
+  fe_mul(zscale, e[3].z, d.z);
+
+  fe_set_zero(acc.x); fe_set_zero(acc.y); fe_set_zero(acc.z);
+  for (int i = 0; i < prm.nops; i++) {
+    const uint32_t op = prm.ops[i];
+    if (op & 0x80u) {
+      gej_dbl(acc, acc);
+    } else {
+      const uint32_t en = op & 3u, comp = (op >> 2) & 1u;
+      fe qx, qy;
+#pragma unroll
+      for (int l = 0; l < 8; l++) { qx.v[l] = tab.get(en, comp, l); qy.v[l] = tab.get(en, 2, l); }
+      if (op & 0x08u) fe_neg(qy, qy);
+      if (op & 0x40u) {
+        acc.x = qx; acc.y = qy; fe_set_u32(acc.z, 1);
+      } else {
+        gej_add_ge(acc, acc, qx, qy);
+      }
+    }
+  }
+  fe_mul(acc.z, acc.z, zscale);
+}
+
+// ---------------------------------------------------------------- K2/K4/K6 body: batch inversion
+// vals[i] <- vals[i]^-1 (0 stays 0) for i = tid, tid+T, tid+2T, ...  Prefix products go to
+// scratch, one Fermat inversion, then the back pass (Montgomery's trick).
+CSP_HD void batch_inv_thread(fe *vals, fe *scratch, uint32_t n, uint32_t T, uint32_t tid) {
+  if (tid >= T || tid >= n) return;
+  fe acc;
+  fe_set_u32(acc, 1);
+  uint32_t last = tid;
+  for (uint64_t i = tid; i < n; i += T) {
+    fe v;
+    load_fe(v, vals + i);
+    store_fe(scratch + i, acc);
+    if (!fe_is_zero(v)) fe_mul(acc, acc, v);
+    last = (uint32_t)i;
+  }
+  fe inv;
+  fe_inv(inv, acc);
+  for (uint32_t i = last;; i -= T) {
+    fe v, pre, out;
+    load_fe(v, vals + i);
+    load_fe(pre, scratch + i);
+    if (fe_is_zero(v)) {
+      fe_set_zero(out);
+    } else {
+      fe_mul(out, inv, pre);
+      fe_mul(inv, inv, v);
+    }
+    store_fe(vals + i, out);
+    if (i == tid) break;
+  }
+}
+
+// ---------------------------------------------------------------- K3 body: hash, t*G, + B_spend
+// in : shared secret S as Jacobian (X, Y) plus Zinv from the batch inversion
+// out: P0 = t*G + B_spend as Jacobian.
+// t*G uses the offset fixed-window table gtab[w][d] = (d * 2^(8w) + r_w) * G (affine, 64 B per
+// entry, 512 KB total, L2-resident): 31 mixed additions, no zero digits, no doublings.  The
+// constant (sum r_w)*G is removed by adding spend_adj = B_spend - (sum r_w)*G instead of B_spend.
+// sx, sy, t_out (optional) receive the affine shared secret and the hash for the intermediates API.
+CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zinv, const ge *gtab, const FinalParams &fp,
+                               fe *sx, fe *sy, fe *t_out) {
+  fe x, y;
+  if (fp.zero_scalar) {
+    fe_set_zero(x); fe_set_zero(y);
+  } else {
+    fe zi2, zi3;
+    fe_sqr(zi2, Zinv);
+    fe_mul(zi3, zi2, Zinv);
+    fe_mul(x, X, zi2);
+    fe_mul(y, Y, zi3);
+    fe_normalize(x);
+    fe_normalize(y);
+  }
+  if (sx) *sx = x;
+  if (sy) *sy = y;
+  fe t;
+  bip352_shared_secret_hash(t, x, y.v[0] & 1u, fp.midstate);
+  if (t_out) *t_out = t;
+  {
+    const ge *q = gtab + (t.v[0] & 0xffu);
+    load_fe_ro(acc.x, &q->x);
+    load_fe_ro(acc.y, &q->y);
+    fe_set_u32(acc.z, 1);
+  }
+  fe qx, qy;
+  {
+    const ge *q = gtab + GTAB_ENTRIES + ((t.v[0] >> 8) & 0xffu);
+    load_fe_ro(qx, &q->x);
+    load_fe_ro(qy, &q->y);
+  }
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  for (int w = 1; w < GTAB_NWIN; w++) {
+    fe nx, ny;
+    if (w + 1 < GTAB_NWIN) {   // prefetch the next window's entry while this addition runs
+      const uint32_t dgt = (t.v[(w + 1) >> 2] >> (((w + 1) & 3) * 8)) & 0xffu;
+      const ge *q = gtab + (size_t)(w + 1) * GTAB_ENTRIES + dgt;
+      load_fe_ro(nx, &q->x);
+      load_fe_ro(ny, &q->y);
+    } else {
+      nx = qx; ny = qy;
+    }
+    gej_add_ge(acc, acc, qx, qy);
+    qx = nx; qy = ny;
+  }
+  if (!fp.spend_adj_inf) gej_add_ge(acc, acc, fp.spend_adj_x, fp.spend_adj_y);
+}
+
+// ---------------------------------------------------------------- K5/K7 bodies
+CSP_HD int64_t upper64(const fe &x_canonical) {   // src/cudasp_gpu.cu:67-71
+  return (int64_t)(((uint64_t)x_canonical.v[7] << 32) | x_canonical.v[6]);
+}
+// base candidate: x0 = X * Zinv^2 (canonical), optionally y0
+CSP_HD int64_t base_candidate(fe &x0, fe *y0, const fe &X, const fe &Y, const fe &Zinv) {
+  fe zi2;
+  fe_sqr(zi2, Zinv);
+  fe_mul(x0, X, zi2);
+  fe_normalize(x0);
+  if (y0) {
+    fe zi3;
+    fe_mul(zi3, zi2, Zinv);
+    fe_mul(*y0, Y, zi3);
+    fe_normalize(*y0);
+  }
+  return upper64(x0);
+}
+// label candidate: int64(x(P0 + L) >> 192) with the affine chord rule and the inverted
+// denominator dinv = (xL - x0)^-1 from the shared inversion   (src/cudasp_gpu.cu:153-172).
+// dinv == 0 marks xL == x0: L = P0 -> tangent rule; L = -P0 -> infinity, whose affine form in the
+// reference is (1, 0), i.e. candidate 0 (gECC ec.h:84-89,584-588).  Rare: private inversion.
+CSP_HD int64_t label_candidate(const fe &x0, const fe &y0, const fe &lx, const fe &ly, const fe &dinv) {
+  fe dy, lam, x;
+  fe_sub(dy, ly, y0);
+  if (fe_is_zero(dinv)) {
+    if (fe_is_zero(dy) && !fe_is_zero(y0)) {
+      fe num, den;
+      fe_sqr(num, x0);
+      fe_lin1<3>(num, num);
+      fe_lin1<2>(den, y0);
+      fe_inv(den, den);
+      fe_mul(lam, num, den);
+      fe_sqr(x, lam);
+      fe_lin2<1, -2>(x, x, x0);
+      fe_normalize(x);
+      return upper64(x);
+    }
+    return 0;
+  }
+  fe_mul(lam, dy, dinv);
+  fe_sqr(x, lam);
+  fe_lin3<1, -1, -1>(x, x, x0, lx);
+  fe_normalize(x);
+  return upper64(x);
+}
+
+}  // namespace csp

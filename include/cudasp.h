@@ -1,0 +1,131 @@
+/* cudasp.h -- C ABI of the B200-native cudasp_scan hot path (libcudasp_b200.so).
+ *
+ * This is the drop-in boundary.  It replaces the reference's internal FFI between the DuckDB
+ * table function and its GPU pipeline:
+ *     void* LaunchBatchScan(...); int RunBatchScanKernels(...); void FreeBatchScanState(void*);
+ *     (reference: src/cudasp_extension.cu:21-52, implemented in src/cudasp_gpu.cu:445-1023)
+ * Plain C types only; every function returns CUDASP_OK (0) or a negative error code and
+ * records a message retrievable with cudasp_last_error().  Unlike the reference, which printf()s
+ * and silently yields no rows on a GPU failure (src/cudasp_extension.cu:325,378), errors are
+ * always reported to the caller.  There is no CPU fallback: without a CUDA device every entry
+ * point that needs one fails with CUDASP_ERR_CUDA.
+ *
+ * Byte layouts are the reference's:
+ *   scan_private_key  32 B little-endian integer          (src/cudasp_extension.cu:77-85)
+ *   points            64 B = x little-endian || y little-endian, no prefix byte   (:56-75)
+ *   outputs           int64 = first 8 bytes of an output's x-only key, big-endian, as signed
+ *   out_offsets       CSR: row r owns outputs[out_offsets[r] .. out_offsets[r+1])   (rows+1 entries;
+ *                     the reference passes offset+length arrays, src/cudasp_gpu.cu:29-41)
+ * Row semantics: a row matches iff  int64(x(P0) >> 192)  or, for any label i,
+ * int64(x(P0 + L_i) >> 192)  is in the row's outputs, where  P0 = t*G + B_spend,
+ * t = int_BE(SHA256(TH||TH||ser(S)||00000000)),  S = scan_sk * tweak_key.
+ */
+#ifndef CUDASP_H
+#define CUDASP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CUDASP_OK 0
+#define CUDASP_ERR_ARG (-1)    /* bad argument (sizes, NULLs, label count ...) */
+#define CUDASP_ERR_CUDA (-2)   /* CUDA runtime error or no device */
+#define CUDASP_ERR_STATE (-3)  /* call not valid in this state (e.g. slot not acquired) */
+#define CUDASP_ERR_KEY (-4)    /* scan key for which no valid ladder schedule exists */
+
+#define CUDASP_MAX_LABELS 64u
+#define CUDASP_MAX_BATCH_ROWS 10000000u /* reference: batch_size <= 10,000,000 (src/cudasp_extension.cu:485) */
+
+typedef struct cudasp_query cudasp_query;
+
+/* Number of visible CUDA devices (reference: cudaGetDeviceCount in CudaspScanState,
+ * src/cudasp_extension.cu:129-132).  Returns 0 when there is none. */
+int cudasp_device_count(void);
+
+/* Last error message of a query handle, or of the calling thread when q == NULL. */
+const char *cudasp_last_error(const cudasp_query *q);
+
+/* Once-per-query setup.  Replaces the per-batch key marshalling of ProcessBatch/LaunchBatchScan
+ * (src/cudasp_extension.cu:277-297, src/cudasp_gpu.cu:445-669) and Solver::initialize
+ * (gECC gsv.h:1094-1122): recodes the fixed scan key (GLV + wNAF), uploads the fixed-base table,
+ * allocates every device/pinned buffer for `batch_rows`-row batches on each listed device.
+ *   devices == NULL  -> use devices 0..n_devices-1;  n_devices == 0 -> all visible devices.
+ *   max_outputs_per_batch == 0 -> 8 * batch_rows (grown on demand by the synchronous call). */
+int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64],
+                        const uint8_t *label_keys /* n_labels * 64 B */, uint32_t n_labels,
+                        const int *devices, int n_devices, uint32_t batch_rows,
+                        uint64_t max_outputs_per_batch, cudasp_query **out);
+
+/* Replaces FreeBatchScanState (src/cudasp_gpu.cu:969-1023).  Waits for in-flight batches. */
+void cudasp_query_destroy(cudasp_query *q);
+
+/* ---- synchronous batch: host buffers in, matching row ids out ------------------------------
+ * The call the reference's ProcessBatch makes per batch (LaunchBatchScan + RunBatchScanKernels +
+ * the flag scan, src/cudasp_extension.cu:308-392), as one function.  Thread-safe: concurrent
+ * callers are spread over the query's devices.  rows may exceed batch_rows (split internally).
+ * match_ids (capacity >= rows) receives the ascending indices of matching rows. */
+int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys /* rows * 64 B */,
+                      const int64_t *outputs, const uint32_t *out_offsets /* rows + 1 */,
+                      uint32_t rows, uint32_t *match_ids, uint32_t *n_matches);
+
+/* ---- streaming: pinned double-buffered staging, async H2D on per-device streams -------------
+ * The host fills a pinned slot directly from its column vectors (what AccumulateInput does into
+ * std::vectors, src/cudasp_extension.cu:154-224), submits it, and collects results later. */
+typedef struct cudasp_slot {
+  uint32_t slot_id;
+  int32_t device;
+  uint8_t *tweak_keys;    /* pinned, cap_rows * 64 B */
+  int64_t *outputs;       /* pinned, cap_outputs */
+  uint32_t *out_offsets;  /* pinned, cap_rows + 1 */
+  uint32_t cap_rows;
+  uint64_t cap_outputs;
+} cudasp_slot;
+
+typedef struct cudasp_result {
+  uint64_t tag;              /* caller's tag from cudasp_submit_slot */
+  uint32_t slot_id;
+  uint32_t rows;
+  uint32_t n_matches;
+  const uint32_t *match_ids; /* pinned; ascending row indices within the slot; valid until release */
+} cudasp_result;
+
+/* Blocks until a staging slot is free (a slot is recycled by cudasp_release_result). */
+int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot);
+/* Enqueue H2D + kernels + D2H for `rows` rows / `n_outputs` outputs of an acquired slot. */
+int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag);
+/* Returns 1 and fills *r when a finished batch is available, 0 when none is finished yet. */
+int cudasp_poll(cudasp_query *q, cudasp_result *r);
+/* Blocks for the oldest in-flight batch; returns 1 with *r filled, or 0 when nothing is in flight. */
+int cudasp_wait(cudasp_query *q, cudasp_result *r);
+/* Hand the slot of a consumed result back to the pool. */
+int cudasp_release_result(cudasp_query *q, const cudasp_result *r);
+
+/* ---- device-resident entry (benchmarks; hosts that already hold columns in HBM) -------------
+ * All pointers are device pointers on `device` (which must be one of the query's devices);
+ * `stream` is a cudaStream_t (0 = the query's own stream for that device).  Asynchronous.
+ * d_match_ids: capacity >= rows; *d_n_matches is reset and then holds the count; ids unordered. */
+int cudasp_scan_device(cudasp_query *q, int device, const uint8_t *d_tweak_keys, const int64_t *d_outputs,
+                       const uint32_t *d_out_offsets, uint32_t rows, uint32_t *d_match_ids,
+                       uint32_t *d_n_matches, void *stream);
+
+/* ---- introspection used by the parity tests and bench.py -----------------------------------
+ * Per-row candidates instead of match flags: cands[r*(1+L) + 0] = base, [.. + 1 + i] = label i. */
+int cudasp_scan_candidates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands);
+/* Per-row intermediates: shared secret S (64 B LE x||y), t (32 B big-endian), P0 (64 B LE). Any may be NULL. */
+int cudasp_scan_intermediates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows,
+                              uint8_t *S_le, uint8_t *t_be, uint8_t *P0_le);
+/* Field KATs on the device: op 0 mul, 1 sqr(a), 2 add, 3 sub, 4 inv(a), 5 normalize(a); n elements of 32 B LE. */
+int cudasp_test_field(int device, int op, const uint8_t *a, const uint8_t *b, uint8_t *out, uint32_t n);
+/* Counters: number of kernel launches issued by this query so far; ladder schedule shape. */
+uint64_t cudasp_launch_count(const cudasp_query *q);
+int cudasp_query_info(const cudasp_query *q, int *n_devices, int *ladder_dbl, int *ladder_add, int *fixed_window_bits,
+                      int *n_labels);
+const char *cudasp_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUDASP_H */

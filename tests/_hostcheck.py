@@ -1,0 +1,112 @@
+"""Loader for tests/hostcheck/libhostcheck.so (TEST INFRASTRUCTURE): the product's host/device row
+functions compiled with g++ so their logic can be checked on the CPU against the oracle."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "hostcheck", "host_check.cpp")
+SO = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck.so")
+CSRC = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "csrc")
+_lib = None
+
+
+def build(force=False):
+    deps = [SRC] + [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
+    if force or not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(d) for d in deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-I", CSRC,
+                               "-Wno-unknown-pragmas", "-o", SO, SRC])
+    return SO
+
+
+def load():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(SO)
+    return _lib
+
+
+def _p(a, t=C.c_uint8):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def _b(b):
+    return np.frombuffer(bytes(b), np.uint8).copy()
+
+
+def field(op, a_list, b_list):
+    lib = load()
+    n = len(a_list)
+    a = _b(b"".join(x.to_bytes(32, "little") for x in a_list))
+    b = _b(b"".join(x.to_bytes(32, "little") for x in b_list))
+    out = np.zeros(32 * n, np.uint8)
+    lib.hc_field(op, _p(a), _p(b), _p(out), n)
+    return [int.from_bytes(out[32 * i:32 * i + 32].tobytes(), "little") for i in range(n)]
+
+
+def glv(k):
+    lib = load()
+    k1, k2 = np.zeros(32, np.uint8), np.zeros(32, np.uint8)
+    n1, n2 = C.c_int(), C.c_int()
+    lib.hc_glv(_p(_b(k.to_bytes(32, "little"))), _p(k1), C.byref(n1), _p(k2), C.byref(n2))
+    a, b = int.from_bytes(k1.tobytes(), "little"), int.from_bytes(k2.tobytes(), "little")
+    return (-a if n1.value else a), (-b if n2.value else b)
+
+
+def plan(sk_le):
+    lib = load()
+    ops = np.zeros(256, np.uint8)
+    v = [C.c_int() for _ in range(5)]
+    lib.hc_plan(_p(_b(sk_le)), _p(ops), *[C.byref(x) for x in v])
+    nops, n_dbl, n_add, zero, regular = [x.value for x in v]
+    return dict(ops=ops[:nops].tolist(), n_dbl=n_dbl, n_add=n_add, zero=bool(zero), regular=bool(regular))
+
+
+def midstate():
+    lib = load()
+    out = np.zeros(8, np.uint32)
+    lib.hc_midstate(_p(out, C.c_uint32))
+    return out.tolist()
+
+
+def ladder(sk_le, points):
+    lib = load()
+    pts = _b(b"".join(points))
+    out = np.zeros(64 * len(points), np.uint8)
+    rc = lib.hc_ladder(_p(_b(sk_le)), _p(pts), len(points), _p(out))
+    assert rc == 0, rc
+    return [out[64 * i:64 * i + 64].tobytes() for i in range(len(points))]
+
+
+def scan_candidates(sk, spend, labels, tweaks, T=7, want_inter=False):
+    lib = load()
+    L = len(labels)
+    tw = _b(b"".join(tweaks))
+    rows = len(tweaks)
+    lab = _b(b"".join(labels)) if L else np.zeros(1, np.uint8)
+    cands = np.zeros((rows, 1 + L), np.int64)
+    S, t, P0 = np.zeros(64 * rows, np.uint8), np.zeros(32 * rows, np.uint8), np.zeros(64 * rows, np.uint8)
+    rc = lib.hc_scan_candidates(_p(_b(sk)), _p(_b(spend)), _p(lab), L, _p(tw), rows, T, _p(cands, C.c_int64),
+                                _p(S) if want_inter else None, _p(t) if want_inter else None, _p(P0) if want_inter else None)
+    if rc:
+        raise RuntimeError("hc_scan_candidates rc=%d" % rc)
+    if want_inter:
+        return cands, S.reshape(rows, 64), t.reshape(rows, 32), P0.reshape(rows, 64)
+    return cands
+
+
+def gtab_entry(w, d):
+    lib = load()
+    out = np.zeros(64, np.uint8)
+    lib.hc_gtab_entry(w, d, _p(out))
+    return out.tobytes()
+
+
+def gtab_offset(w):
+    lib = load()
+    out = np.zeros(32, np.uint8)
+    lib.hc_gtab_offset(w, _p(out))
+    return int.from_bytes(out.tobytes(), "little")

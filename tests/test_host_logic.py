@@ -1,0 +1,151 @@
+"""CPU: the product's own row functions / host precompute (compiled with g++ from
+duckdb-cudasp-extension_b200/csrc via tests/hostcheck) against the golden vectors and the oracle."""
+import hashlib
+import random
+
+import numpy as np
+import pytest
+
+from oracle import c_oracle as CO
+from oracle import ref_scan as R
+from tests import _hostcheck as H
+
+P, N = R.P, R.N
+LAMBDA = 0x5363AD4CC05C30E0A5261C028812645A122E22EA20816678DF02967C1B23BD72
+
+
+def I(h):
+    return int(h, 16)
+
+
+def test_field_kats(golden):
+    ks = golden["field"]
+    a, b = [I(k["a"]) for k in ks], [I(k["b"]) for k in ks]
+    assert H.field(0, a, b) == [I(k["mul"]) for k in ks]
+    assert H.field(2, a, b) == [I(k["add"]) for k in ks]
+    assert H.field(3, a, b) == [I(k["sub"]) for k in ks]
+    assert H.field(1, a, a) == [x * x % P for x in a]
+    nz = [(x, I(k["inv"])) for x, k in zip(a, ks) if x]
+    assert H.field(4, [x for x, _ in nz], [0] * len(nz)) == [i for _, i in nz]
+
+
+def test_field_weak_inputs_and_edges():
+    """Inputs in [p, 2^256) are legal weakly-reduced values; results must be right mod p."""
+    rng = random.Random(7)
+    top = (1 << 256) - 1
+    edge = [0, 1, P - 1, P, P + 1, top, top - 1, (1 << 256) - (1 << 32), (1 << 255), 0x1000003D0, 0x1000003D1, 0x1000003D2,
+            top - 0x1000003D1, (1 << 224) - 1, ((1 << 256) - 1) ^ ((1 << 128) - 1)]
+    vals = edge + [rng.randrange(1 << 256) for _ in range(50)]
+    a = [x for x in vals for _ in vals]
+    b = [y for _ in vals for y in vals]
+    assert H.field(0, a, b) == [x * y % P for x, y in zip(a, b)]
+    assert H.field(1, a, a) == [x * x % P for x in a]
+    assert H.field(2, a, b) == [(x + y) % P for x, y in zip(a, b)]
+    assert H.field(3, a, b) == [(x - y) % P for x, y in zip(a, b)]
+    assert H.field(6, a, b) == [(-x) % P for x in a]
+    assert H.field(7, a, b) == [(x - 8 * y) % P for x, y in zip(a, b)]
+    assert H.field(8, a, b) == [(x - 3 * y) % P for x, y in zip(a, b)]
+    assert H.field(9, a, b) == [(4 * x - y) % P for x, y in zip(a, b)]
+    assert H.field(5, vals, vals) == [x % P for x in vals]
+
+
+def test_glv_split():
+    rng = random.Random(11)
+    for k in [1, 2, 3, N - 1, N - 2, LAMBDA, LAMBDA + 1, (1 << 128), (1 << 255) % N] + [rng.randrange(1, N) for _ in range(200)]:
+        k1, k2 = H.glv(k)
+        assert (k1 + k2 * LAMBDA - k) % N == 0
+        assert abs(k1) < (1 << 129) and abs(k2) < (1 << 129)
+
+
+def test_midstate_matches_hashlib():
+    # chaining value after TH||TH: check by finishing a hash by hand is overkill; compare with a
+    # pure-Python compression of the same block instead
+    th = hashlib.sha256(b"BIP0352/SharedSecret").digest()
+    from tests._sha_ref import compress_block, IV
+    assert H.midstate() == compress_block(list(IV), th + th)
+
+
+def test_plan_shape_and_regularity():
+    rng = random.Random(5)
+    for k in [1, 2, 3, 5, 7, 9, 15, 16, 17, N - 1, N + 1, (1 << 256) - 1] + [rng.randrange(1, 1 << 256) for _ in range(100)]:
+        p = H.plan(k.to_bytes(32, "little"))
+        assert p["regular"] and not p["zero"]
+        assert p["n_dbl"] <= 130 and p["n_add"] <= 60
+        assert p["ops"][0] & 0x40 and not any(o & 0x40 for o in p["ops"][1:])
+    assert H.plan((0).to_bytes(32, "little"))["zero"] and H.plan(N.to_bytes(32, "little"))["zero"]
+
+
+@pytest.mark.parametrize("key", ["pmul_seed42", "pmul_gpu_dumps", "pmul_batch_seed42"])
+def test_ladder_kats(golden, key):
+    for k in golden[key]:
+        pt = R.encode_point((I(k["x"]), I(k["y"])))
+        out = H.ladder(I(k["s"]).to_bytes(32, "little"), [pt])[0]
+        assert R.parse_point(out) == (I(k["rx"]), I(k["ry"]))
+
+
+def test_ladder_g_multiples(golden):
+    g = R.encode_point(R.G)
+    for k in golden["g_multiples"]:
+        out = H.ladder(I(k["k"]).to_bytes(32, "little"), [g])[0]
+        assert R.parse_point(out) == (I(k["rx"]), I(k["ry"]))
+
+
+def test_gtab_entries():
+    for w, d in [(0, 0), (0, 1), (0, 255), (1, 0), (5, 77), (31, 255)]:
+        want = R.pt_mul((d << (8 * w)) + H.gtab_offset(w), R.G)
+        assert R.parse_point(H.gtab_entry(w, d)) == want
+
+
+def test_pipeline_kats(golden):
+    for k in golden["pipeline"]:
+        sk = I(k["sk"]).to_bytes(32, "little")
+        pb = lambda xy: R.encode_point((I(xy[0]), I(xy[1])))
+        cands, S, t, P0 = H.scan_candidates(sk, pb(k["spend"]), [pb(l) for l in k["labels"]], [pb(k["tweak"])], T=1, want_inter=True)
+        assert cands[0].tolist() == k["cands"]
+        assert R.parse_point(S[0].tobytes()) == (I(k["S"][0]), I(k["S"][1]))
+        assert t[0].tobytes().hex() == k["t"]
+        assert R.parse_point(P0[0].tobytes()) == (I(k["P0"][0]), I(k["P0"][1]))
+
+
+def test_sql_rows(golden):
+    rows = golden["sql"]["test_data"]
+    for q in golden["sql"]["queries"]:
+        if q["table"] != "test_data" or q["select"] != "height":
+            continue
+        row = [r for r in rows if r["height"] == q["expect"]][0]
+        cands = H.scan_candidates(bytes.fromhex(q["scan_sk"]), bytes.fromhex(q["spend"]), [bytes.fromhex(l) for l in q["labels"]],
+                                  [bytes.fromhex(row["tweak"])])
+        assert set(cands[0].tolist()) & set(row["outputs"])
+
+
+def test_random_rows_vs_c_oracle():
+    rng = random.Random(99)
+    for L in (0, 3):
+        sk = rng.randrange(1, N).to_bytes(32, "little")
+        spend = R.encode_point(R.pt_mul(rng.randrange(1, N), R.G))
+        labels = [R.encode_point(R.pt_mul(rng.randrange(1, N), R.G)) for _ in range(L)]
+        base = R.pt_mul(rng.randrange(1, N), R.G)
+        step = R.pt_mul(rng.randrange(1, N), R.G)
+        tweaks, cur = [], base
+        for _ in range(37):
+            tweaks.append(R.encode_point(cur))
+            cur = R.pt_add(cur, step)
+        got = H.scan_candidates(sk, spend, labels, tweaks, T=5)
+        _, want = CO.scan(sk, spend, labels, np.frombuffer(b"".join(tweaks), np.uint8).reshape(-1, 64), None, None, want_cands=True)
+        assert np.array_equal(got, want)
+
+
+def test_label_edge_cases_and_zero_scalar():
+    sk, spend = R.encode_scalar(12345), R.encode_point(R.G)
+    tw = R.encode_point(R.pt_mul(99, R.G))
+    P0 = R.row_intermediates(12345, R.parse_point(tw), R.G)["P0"]
+    neg = (P0[0], P - P0[1])
+    other = R.pt_mul(777, R.G)
+    labels = [R.encode_point(neg), R.encode_point(P0), R.encode_point(other)]
+    got = H.scan_candidates(sk, spend, labels, [tw, tw], T=2)
+    want = R.row_candidates(12345, R.parse_point(tw), R.G, [neg, P0, other])
+    assert got[0].tolist() == want and got[1].tolist() == want
+    # scalar = 0 and scalar = n: the reference's all-zero shared secret
+    for k in (0, N):
+        z = R.row_intermediates(0, R.parse_point(tw), R.G)
+        assert H.scan_candidates(k.to_bytes(32, "little"), spend, [], [tw])[0].tolist() == z["cands"]
