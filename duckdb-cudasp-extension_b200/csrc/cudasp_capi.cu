@@ -406,3 +406,238 @@ int finish(cudasp_query *q, Slot *s, uint32_t *n_matches) {
 }
 
 }  // namespace
+
+// =====================================================================================
+extern "C" {
+
+// ---- streaming API --------------------------------------------------------------------
+int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
+  if (!q || !slot) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  Slot *s = acquire_blocking(q);
+  slot->slot_id = s->id;
+  slot->device = q->devs[s->dev_index].device;
+  slot->tweak_keys = s->h_tweaks;
+  slot->outputs = s->h_outputs;
+  slot->out_offsets = s->h_off;
+  slot->cap_rows = s->cap_rows;
+  slot->cap_outputs = s->cap_outputs;
+  return CUDASP_OK;
+}
+
+int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag) {
+  if (!q || !slot || slot->slot_id >= q->all_slots.size()) return fail(q, CUDASP_ERR_ARG, "bad slot");
+  Slot *s = q->all_slots[slot->slot_id];
+  if (s->state != 1) return fail(q, CUDASP_ERR_STATE, "slot was not acquired");
+  if (rows > s->cap_rows || n_outputs > s->cap_outputs) return fail(q, CUDASP_ERR_ARG, "rows/outputs exceed the slot capacity");
+  if (rows && s->h_off[rows] != n_outputs) return fail(q, CUDASP_ERR_ARG, "out_offsets[rows] != n_outputs");
+  int rc = submit(q, s, rows, n_outputs, tag);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(q->mu);
+  s->state = 2;
+  q->inflight.push_back(s);
+  return CUDASP_OK;
+}
+
+static int take_result(cudasp_query *q, cudasp_result *r, bool block) {
+  if (!q || !r) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  Slot *s = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(q->mu);
+    if (q->inflight.empty()) return 0;
+    s = q->inflight.front();
+    if (!block) {
+      cudaSetDevice(q->devs[s->dev_index].device);
+      cudaError_t e = cudaEventQuery(s->done);
+      if (e == cudaErrorNotReady) return 0;
+      if (e != cudaSuccess) { q->err = cudaGetErrorString(e); tl_err = q->err; return CUDASP_ERR_CUDA; }
+    }
+    q->inflight.pop_front();
+    s->state = 3;
+  }
+  uint32_t n = 0;
+  int rc = finish(q, s, &n);
+  if (rc) return rc;
+  r->tag = s->tag;
+  r->slot_id = s->id;
+  r->rows = s->rows;
+  r->n_matches = n;
+  r->match_ids = s->h_result + 1;
+  return 1;
+}
+int cudasp_poll(cudasp_query *q, cudasp_result *r) { return take_result(q, r, false); }
+int cudasp_wait(cudasp_query *q, cudasp_result *r) { return take_result(q, r, true); }
+
+int cudasp_release_result(cudasp_query *q, const cudasp_result *r) {
+  if (!q || !r || r->slot_id >= q->all_slots.size()) return fail(q, CUDASP_ERR_ARG, "bad result");
+  Slot *s = q->all_slots[r->slot_id];
+  if (s->state != 3) return fail(q, CUDASP_ERR_STATE, "result was not handed out");
+  release_slot(q, s);
+  return CUDASP_OK;
+}
+
+// ---- synchronous batch ----------------------------------------------------------------
+int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t *outputs, const uint32_t *out_offsets,
+                      uint32_t rows, uint32_t *match_ids, uint32_t *n_matches) {
+  if (!q || !n_matches) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  *n_matches = 0;
+  if (rows == 0) return CUDASP_OK;
+  if (!tweak_keys || !match_ids) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  if (out_offsets && !outputs && out_offsets[rows] != out_offsets[0]) return fail(q, CUDASP_ERR_ARG, "outputs is NULL");
+  struct Pending { Slot *s; uint32_t base; };
+  std::deque<Pending> pending;
+  uint32_t total = 0;
+  int rc = 0;
+  auto collect = [&](Pending p) -> int {
+    uint32_t n = 0;
+    int r = finish(q, p.s, &n);
+    if (!r) {
+      for (uint32_t i = 0; i < n; i++) match_ids[total + i] = p.base + p.s->h_result[1 + i];
+      total += n;
+    }
+    release_slot(q, p.s);
+    return r;
+  };
+  for (uint32_t base = 0; base < rows && !rc; base += q->batch_rows) {
+    const uint32_t cnt = std::min<uint32_t>(q->batch_rows, rows - base);
+    Slot *s = nullptr;
+    while (!s) {
+      {
+        std::lock_guard<std::mutex> lk(q->mu);
+        s = try_acquire_locked(q);
+      }
+      if (s) break;
+      if (!pending.empty()) {          // recycle our own oldest batch (results stay in row order)
+        Pending p = pending.front();
+        pending.pop_front();
+        rc = collect(p);
+        if (rc) break;
+      } else {
+        s = acquire_blocking(q);
+      }
+    }
+    if (rc) break;
+    s->internal = true;
+    const uint32_t o0 = out_offsets ? out_offsets[base] : 0;
+    const uint64_t no = out_offsets ? (uint64_t)(out_offsets[base + cnt] - o0) : 0;
+    if (no > s->cap_outputs) {
+      cudaSetDevice(q->devs[s->dev_index].device);
+      cudaStreamSynchronize(s->stream);
+      rc = alloc_slot_outputs(q, *s, no + no / 4);
+      if (rc) { release_slot(q, s); break; }
+    }
+    memcpy(s->h_tweaks, tweak_keys + (size_t)base * 64, (size_t)cnt * 64);
+    if (out_offsets) {
+      for (uint32_t i = 0; i <= cnt; i++) s->h_off[i] = out_offsets[base + i] - o0;
+      if (no) memcpy(s->h_outputs, outputs + o0, no * 8);
+    } else {
+      memset(s->h_off, 0, ((size_t)cnt + 1) * 4);
+    }
+    rc = submit(q, s, cnt, no, 0);
+    if (rc) { release_slot(q, s); break; }
+    pending.push_back({s, base});
+  }
+  while (!pending.empty()) {
+    Pending p = pending.front();
+    pending.pop_front();
+    int r = collect(p);
+    if (!rc) rc = r;
+  }
+  *n_matches = total;
+  return rc;
+}
+
+// ---- device-resident entry ------------------------------------------------------------
+int cudasp_scan_device(cudasp_query *q, int device, const uint8_t *d_tweak_keys, const int64_t *d_outputs,
+                       const uint32_t *d_out_offsets, uint32_t rows, uint32_t *d_match_ids, uint32_t *d_n_matches,
+                       void *stream) {
+  if (!q) return fail(q, CUDASP_ERR_ARG, "NULL query");
+  DevCtx *dc = nullptr;
+  for (DevCtx &d : q->devs) if (d.device == device) dc = &d;
+  if (!dc) return fail(q, CUDASP_ERR_ARG, "device is not part of this query");
+  if (rows > q->batch_rows) return fail(q, CUDASP_ERR_ARG, "rows exceed batch_rows (split the call)");
+  if (rows && (!d_tweak_keys || !d_match_ids || !d_n_matches)) return fail(q, CUDASP_ERR_ARG, "NULL device pointer");
+  CU(q, cudaSetDevice(device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : dc->own_stream;
+  // borrow the scratch of one of the device's slots, round robin; ordering between users of the
+  // same scratch is enforced with its free_evt, so any stream may be used.
+  Workspace *w;
+  {
+    std::lock_guard<std::mutex> lk(q->mu);
+    w = &dc->slots[dc->next_ws++ % dc->slots.size()]->ws;
+  }
+  CU(q, cudaStreamWaitEvent(st, w->free_evt, 0));
+  int rc = launch_pipeline(q, *dc, *w, d_tweak_keys, d_outputs, d_out_offsets, rows, d_match_ids, d_n_matches, st, nullptr,
+                           nullptr, nullptr, nullptr);
+  if (rc) return rc;
+  CU(q, cudaEventRecord(w->free_evt, st));
+  return CUDASP_OK;
+}
+
+// ---- introspection --------------------------------------------------------------------
+static int scan_debug(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands, uint8_t *S_le, uint8_t *t_be,
+                      uint8_t *P0_le) {
+  if (!q || (rows && !tweak_keys)) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  const uint32_t L = q->n_labels;
+  for (uint32_t base = 0; base < rows; base += q->batch_rows) {
+    const uint32_t cnt = std::min<uint32_t>(q->batch_rows, rows - base);
+    Slot *s = acquire_blocking(q);
+    DevCtx &dc = q->devs[s->dev_index];
+    int rc = 0;
+    int64_t *d_c = nullptr;
+    uint8_t *d_S = nullptr, *d_t = nullptr, *d_P = nullptr;
+    auto body = [&]() -> int {
+      CU(q, cudaSetDevice(dc.device));
+      if (cands) CU(q, cudaMalloc(&d_c, (size_t)cnt * (1 + L) * 8));
+      if (S_le) CU(q, cudaMalloc(&d_S, (size_t)cnt * 64));
+      if (t_be) CU(q, cudaMalloc(&d_t, (size_t)cnt * 32));
+      if (P0_le) CU(q, cudaMalloc(&d_P, (size_t)cnt * 64));
+      CU(q, cudaMemcpyAsync(s->d_tweaks, tweak_keys + (size_t)base * 64, (size_t)cnt * 64, cudaMemcpyHostToDevice, s->stream));
+      CU(q, cudaStreamWaitEvent(s->stream, s->ws.free_evt, 0));
+      int r = launch_pipeline(q, dc, s->ws, s->d_tweaks, nullptr, nullptr, cnt, nullptr, nullptr, s->stream, d_c, d_S, d_t, d_P);
+      if (r) return r;
+      CU(q, cudaEventRecord(s->ws.free_evt, s->stream));
+      if (cands) CU(q, cudaMemcpyAsync(cands + (size_t)base * (1 + L), d_c, (size_t)cnt * (1 + L) * 8, cudaMemcpyDeviceToHost, s->stream));
+      if (S_le) CU(q, cudaMemcpyAsync(S_le + (size_t)base * 64, d_S, (size_t)cnt * 64, cudaMemcpyDeviceToHost, s->stream));
+      if (t_be) CU(q, cudaMemcpyAsync(t_be + (size_t)base * 32, d_t, (size_t)cnt * 32, cudaMemcpyDeviceToHost, s->stream));
+      if (P0_le) CU(q, cudaMemcpyAsync(P0_le + (size_t)base * 64, d_P, (size_t)cnt * 64, cudaMemcpyDeviceToHost, s->stream));
+      CU(q, cudaStreamSynchronize(s->stream));
+      return 0;
+    };
+    rc = body();
+    cudaFree(d_c); cudaFree(d_S); cudaFree(d_t); cudaFree(d_P);
+    release_slot(q, s);
+    if (rc) return rc;
+  }
+  return CUDASP_OK;
+}
+int cudasp_scan_candidates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands) {
+  if (!cands) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  return scan_debug(q, tweak_keys, rows, cands, nullptr, nullptr, nullptr);
+}
+int cudasp_scan_intermediates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, uint8_t *S_le, uint8_t *t_be,
+                              uint8_t *P0_le) {
+  return scan_debug(q, tweak_keys, rows, nullptr, S_le, t_be, P0_le);
+}
+
+int cudasp_test_field(int device, int op, const uint8_t *a, const uint8_t *b, uint8_t *out, uint32_t n) {
+  if (!a || !b || !out) return fail(nullptr, CUDASP_ERR_ARG, "NULL argument");
+  if (n == 0) return CUDASP_OK;
+  fe *da = nullptr, *db = nullptr, *dout = nullptr;
+  auto body = [&]() -> int {
+    CU(nullptr, cudaSetDevice(device));
+    CU(nullptr, cudaMalloc(&da, (size_t)n * 32));
+    CU(nullptr, cudaMalloc(&db, (size_t)n * 32));
+    CU(nullptr, cudaMalloc(&dout, (size_t)n * 32));
+    CU(nullptr, cudaMemcpy(da, a, (size_t)n * 32, cudaMemcpyHostToDevice));
+    CU(nullptr, cudaMemcpy(db, b, (size_t)n * 32, cudaMemcpyHostToDevice));
+    k_test_field<<<(n + 127) / 128, 128>>>(op, da, db, dout, n);
+    CU(nullptr, cudaGetLastError());
+    CU(nullptr, cudaMemcpy(out, dout, (size_t)n * 32, cudaMemcpyDeviceToHost));
+    return 0;
+  };
+  int rc = body();
+  cudaFree(da); cudaFree(db); cudaFree(dout);
+  return rc;
+}
+
+}  // extern "C"

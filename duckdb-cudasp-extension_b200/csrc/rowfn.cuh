@@ -3,7 +3,7 @@
 // The kernels in kernels.cuh are thin wrappers (thread <-> row mapping, memory layout, match
 // compaction) around these functions; tests/hostcheck compiles the very same functions with g++
 // so that the schedule logic (GLV/wNAF op list, isomorphic odd-multiples table, offset fixed-base
-// windows, chord/tangent label rule, batch inversion) is verified on the CPU against the oracle
+// windows, chord/tangent label rule, batch inversion) is verified on the CPU against the reference vectors
 // before any GPU time is spent.  That host build is test infrastructure only: the C ABI never
 // calls it and has no CPU path.
 #pragma once

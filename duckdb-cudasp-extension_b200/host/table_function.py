@@ -1,0 +1,191 @@
+"""Host-side mirror of the reference's DuckDB table function `cudasp_scan` above the C ABI.
+
+Same names, argument meaning, NULL handling and error texts as
+/root/reference/src/cudasp_extension.cu (Bind :420-509, AccumulateInput :154-224, ProcessBatch
+:226-410, in-out / final :534-624), so the parity tests read like test/sql/cudasp.test.  The real
+DuckDB shim (C++, same C ABI) is in ../duckdb_ext/; DuckDB itself is not available to Python in
+this image, so this module is what the test-suite drives.
+
+    cudasp_scan(rows, scan_private_key, spend_public_key, label_keys, batch_size=300000)
+        rows: iterable of (txid BLOB, height INTEGER, tweak_key BLOB, outputs BIGINT[]) with None = NULL
+        -> list of (txid, height, tweak_key) for matching rows
+"""
+from __future__ import annotations
+
+from typing import Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .binding import CudaspError, Query
+
+TWEAK_KEY_SIZE = 64   # CudaspScanBindData::TWEAK_KEY_SIZE  (src/cudasp_extension.cu:90)
+SCALAR_SIZE = 32      # CudaspScanBindData::SCALAR_SIZE     (:91)
+STANDARD_VECTOR_SIZE = 2048
+
+
+class InvalidInputException(ValueError):
+    """duckdb::InvalidInputException stand-in."""
+
+
+class IOException(RuntimeError):
+    """Raised for GPU failures (the reference swallows them, src/cudasp_extension.cu:325,378)."""
+
+
+class CudaspScanBindData:
+    def __init__(self, scan_private_key: bytes, spend_public_key: bytes, label_keys: List[bytes], batch_size: int):
+        self.scan_private_key_data = scan_private_key
+        self.spend_public_key_data = spend_public_key
+        self.label_keys_data = label_keys
+        self.batch_size = batch_size
+        self.return_types = ["BLOB", "INTEGER", "BLOB"]
+        self.names = ["txid", "height", "tweak_key"]
+
+
+def CudaspScanBind(inputs: Sequence, named_parameters: Optional[dict] = None) -> CudaspScanBindData:
+    """src/cudasp_extension.cu:420-509 -- same checks, same messages."""
+    named_parameters = named_parameters or {}
+    if len(inputs) != 4:
+        raise InvalidInputException("cudasp_scan requires 4 arguments: TABLE, scan_private_key BLOB, spend_public_key BLOB, and label_keys LIST[BLOB]")
+    _, scan_private_key, spend_public_key, label_keys = inputs
+    if not isinstance(scan_private_key, (bytes, bytearray)):
+        raise InvalidInputException("Second argument must be a BLOB (32-byte scan_private_key)")
+    if len(scan_private_key) != SCALAR_SIZE:
+        raise InvalidInputException("scan_private_key must be exactly 32 bytes, got %d bytes" % len(scan_private_key))
+    if not isinstance(spend_public_key, (bytes, bytearray)):
+        raise InvalidInputException("Third argument must be a BLOB (64-byte spend_public_key)")
+    if len(spend_public_key) != TWEAK_KEY_SIZE:
+        raise InvalidInputException("spend_public_key must be exactly 64 bytes, got %d bytes" % len(spend_public_key))
+    if not isinstance(label_keys, (list, tuple)):
+        raise InvalidInputException("Fourth argument must be a LIST[BLOB] (label keys)")
+    labels = []
+    for k in label_keys:
+        if not isinstance(k, (bytes, bytearray)):
+            raise InvalidInputException("All elements in label_keys must be BLOBs")
+        if len(k) != TWEAK_KEY_SIZE:
+            raise InvalidInputException("Each label key must be exactly 64 bytes, got %d bytes" % len(k))
+        labels.append(bytes(k))
+    batch_size = 300000
+    if "batch_size" in named_parameters:
+        v = named_parameters["batch_size"]
+        if isinstance(v, bool) or not isinstance(v, (int, np.integer)):
+            raise InvalidInputException("batch_size parameter must be an INTEGER")
+        if v <= 0:
+            raise InvalidInputException("batch_size must be positive, got %d" % v)
+        if v > 10000000:
+            raise InvalidInputException("batch_size too large (max 10,000,000), got %d" % v)
+        batch_size = int(v)
+    return CudaspScanBindData(bytes(scan_private_key), bytes(spend_public_key), labels, batch_size)
+
+
+class CudaspScanLocalState:
+    """Per-thread accumulation (src/cudasp_extension.cu:106-120), columnar instead of std::string per row."""
+
+    def __init__(self):
+        self.accumulated_txids: List[bytes] = []
+        self.accumulated_heights: List[int] = []
+        self.accumulated_tweak_keys: List[bytes] = []
+        self.accumulated_outputs: List[int] = []
+        self.accumulated_output_offsets: List[int] = [0]
+        self.finalized = False
+
+
+class CudaspScanState:
+    """Global state (src/cudasp_extension.cu:122-152): owns the C-ABI query handle and the result vectors."""
+
+    def __init__(self, bind_data: CudaspScanBindData, devices: Optional[Sequence[int]] = None):
+        try:
+            self.query = Query(bind_data.scan_private_key_data, bind_data.spend_public_key_data, bind_data.label_keys_data,
+                               devices=devices, batch_rows=bind_data.batch_size)
+        except CudaspError as e:
+            raise IOException(str(e))
+        self.output_txids: List[bytes] = []
+        self.output_heights: List[int] = []
+        self.output_tweak_keys: List[bytes] = []
+        self.output_position = 0
+
+    def close(self):
+        self.query.close()
+
+
+def AccumulateInput(local_state: CudaspScanLocalState, chunk: Iterable[Tuple]) -> None:
+    """src/cudasp_extension.cu:154-224: drop rows with NULL txid/height/tweak_key; NULL list -> length 0;
+    NULL children skipped."""
+    for txid, height, tweak_key, outputs in chunk:
+        if txid is None or height is None or tweak_key is None:
+            continue
+        local_state.accumulated_txids.append(bytes(txid))
+        local_state.accumulated_heights.append(int(height))
+        local_state.accumulated_tweak_keys.append(bytes(tweak_key))
+        if outputs is not None:
+            local_state.accumulated_outputs.extend(int(o) for o in outputs if o is not None)
+        local_state.accumulated_output_offsets.append(len(local_state.accumulated_outputs))
+
+
+def ProcessBatch(local_state: CudaspScanLocalState, bind_data: CudaspScanBindData, global_state: CudaspScanState) -> None:
+    """src/cudasp_extension.cu:226-410: one C-ABI call instead of LaunchBatchScan/RunBatchScanKernels/flag scan."""
+    n = len(local_state.accumulated_txids)
+    if n == 0:
+        return
+    # a tweak_key that is not 64 bytes can never match (the reference reads out of bounds): give it an
+    # all-zero point and mask the row afterwards
+    bad = [i for i, t in enumerate(local_state.accumulated_tweak_keys) if len(t) != TWEAK_KEY_SIZE]
+    tw = np.zeros((n, 64), np.uint8)
+    good = [t if len(t) == TWEAK_KEY_SIZE else b"\0" * 64 for t in local_state.accumulated_tweak_keys]
+    tw[:] = np.frombuffer(b"".join(good), np.uint8).reshape(n, 64)
+    outputs = np.array(local_state.accumulated_outputs, dtype=np.int64)
+    offsets = np.array(local_state.accumulated_output_offsets, dtype=np.uint32)
+    try:
+        ids = global_state.query.scan_batch(tw, outputs, offsets)
+    except CudaspError as e:
+        raise IOException(str(e))
+    badset = set(bad)
+    for i in ids.tolist():
+        if i in badset:
+            continue
+        global_state.output_txids.append(local_state.accumulated_txids[i])
+        global_state.output_heights.append(local_state.accumulated_heights[i])
+        global_state.output_tweak_keys.append(local_state.accumulated_tweak_keys[i])
+    local_state.__init__()
+
+
+def CudaspScanFunction(bind_data, global_state, local_state, chunk) -> str:
+    """in_out_function (src/cudasp_extension.cu:534-552): accumulate, cut a batch when full, emit nothing."""
+    AccumulateInput(local_state, chunk)
+    if len(local_state.accumulated_txids) >= bind_data.batch_size:
+        ProcessBatch(local_state, bind_data, global_state)
+    return "NEED_MORE_INPUT"
+
+
+def CudaspScanFinalFunction(bind_data, global_state, local_state):
+    """in_out_function_final (src/cudasp_extension.cu:554-624): flush, then stream the results out in
+    STANDARD_VECTOR_SIZE chunks."""
+    if not local_state.finalized:
+        ProcessBatch(local_state, bind_data, global_state)
+        local_state.finalized = True
+    while global_state.output_position < len(global_state.output_txids):
+        a = global_state.output_position
+        b = min(a + STANDARD_VECTOR_SIZE, len(global_state.output_txids))
+        global_state.output_position = b
+        yield list(zip(global_state.output_txids[a:b], global_state.output_heights[a:b], global_state.output_tweak_keys[a:b]))
+
+
+def cudasp_scan(rows: Iterable[Tuple], scan_private_key, spend_public_key, label_keys, devices=None, **named_parameters):
+    """SELECT * FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM rows), sk, spend, labels, batch_size := N)"""
+    bind_data = CudaspScanBind([rows, scan_private_key, spend_public_key, label_keys], named_parameters)
+    global_state = CudaspScanState(bind_data, devices)
+    local_state = CudaspScanLocalState()
+    try:
+        chunk = []
+        for r in rows:
+            chunk.append(r)
+            if len(chunk) == STANDARD_VECTOR_SIZE:
+                CudaspScanFunction(bind_data, global_state, local_state, chunk)
+                chunk = []
+        if chunk:
+            CudaspScanFunction(bind_data, global_state, local_state, chunk)
+        out = []
+        for part in CudaspScanFinalFunction(bind_data, global_state, local_state):
+            out.extend(part)
+        return out
+    finally:
+        global_state.close()

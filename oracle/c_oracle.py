@@ -40,6 +40,8 @@ def load():
         lib.oracle_pt_add.restype = C.c_int
         lib.oracle_fe_op.argtypes = [C.c_int, u8p, u8p, u8p]
         lib.oracle_fe_op.restype = C.c_int
+        lib.oracle_gen_chain.argtypes = [u8p, u8p, C.c_uint32, u8p]
+        lib.oracle_gen_chain.restype = C.c_int
         lib.oracle_tagged_hash.argtypes = [u8p, C.c_uint32, u8p]
         lib.oracle_tagged_hash.restype = None
         _lib = lib
@@ -121,3 +123,12 @@ def tagged_hash(msg: bytes) -> bytes:
     out = np.zeros(32, np.uint8)
     lib.oracle_tagged_hash(_p8(_buf(msg)), len(msg), _p8(out))
     return out.tobytes()
+
+
+def gen_chain(p0: bytes, q: bytes, n: int) -> np.ndarray:
+    """uint8 [n,64]: p0 + i*q for i < n (valid curve points)."""
+    lib = load()
+    out = np.zeros((max(n, 1), 64), np.uint8)
+    rc = lib.oracle_gen_chain(_p8(_buf(p0)), _p8(_buf(q)), n, _p8(out))
+    assert rc == 0
+    return out[:n]
