@@ -1,0 +1,274 @@
+#!/usr/bin/env python3
+"""bench.py -- cudasp_scan rows/s on N B200s (one process per GPU), with roofline and CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rows R] [--labels L]
+
+Workload (BASELINE.json configs[1]): 1 M-row synthetic tweak table (1-week shape), no labels,
+batch_size = 300000, per GPU (weak scaling: every rank scans its own table, no collective on the
+data path).  A "step" is one pass of the whole table through the hot path.
+  value  rows/s with the table already resident in HBM (cudasp_scan_device on torch's current stream,
+         CUDA events, L2 flushed between steps, max over ranks)
+  e2e    rows/s through the public host call cudasp_scan_batch with HOST buffers: memcpy into pinned
+         staging, async H2D, kernels, D2H of the match ids -- all inside the timed region
+  roofline  integer-multiply bound: achieved IMAD32 lane-ops/s of the dominant kernel
+         (k_ladder) = rows * 168786 / its CUDA-event time, against the IMAD32 peak measured by
+         tools/imad_peak on this box (fallback: profiles/r01_imad_peak.json)
+  cpu_baseline  the oracle's C port of the reference algorithm on the host cores, bounded sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+W32_BASE, W32_PER_LABEL = 231526, 674          # IMAD32 lane-ops per row
+W32_LADDER = 2 * (666 * 73 + 795 * 45)         # stage A alone = 168786
+SEED = 352002
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=1000000)
+    ap.add_argument("--labels", type=int, default=0)
+    ap.add_argument("--batch", type=int, default=300000)
+    ap.add_argument("--streams", type=int, default=2)
+    return ap.parse_args()
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    def __init__(self, gpu):
+        super().__init__(daemon=True)
+        self.gpu, self.samples, self.stop_flag, self.proc = gpu, [], False, None
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            for line in self.proc.stdout:
+                self.samples.append([x.strip() for x in line.split(",")])
+                if self.stop_flag:
+                    break
+        except Exception:
+            pass
+
+    def finish(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(int(s[0]) for s in self.samples if s and s[0].isdigit())
+        mx = max([int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()] or [0])
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
+
+
+def measured_imad_peak():
+    """IMAD32 lane-ops/s: run tools/imad_peak on this GPU if the binary travelled, else the committed profile."""
+    exe = os.path.join(ROOT, "tools", "imad_peak")
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
+        return float(json.loads(out)["imad_lo"]["lane_ops_per_s"]), "measured live by tools/imad_peak (mad.lo.u32)"
+    except Exception:
+        with open(os.path.join(ROOT, "profiles", "r01_imad_peak.json")) as f:
+            return float(json.load(f)["imad_lo"]["lane_ops_per_s"]), "profiles/r01_imad_peak.json (tools/imad_peak, earlier call)"
+
+
+def cpu_sample(T, rows_sample, threads):
+    from oracle import c_oracle as CO
+    n = min(rows_sample, T["tweaks"].shape[0])
+    off = T["offsets"][: n + 1]
+    t0 = time.perf_counter()
+    flags, _ = CO.scan(T["sk"], T["spend"], T["labels"], T["tweaks"][:n], T["outputs"], off, threads=threads)
+    dt = time.perf_counter() - t0
+    return n / dt, n, dt, flags
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    L = args.labels
+    w32 = W32_BASE + W32_PER_LABEL * L
+    workload = "%d-row synthetic tweak table (1-week shape), %d labels, batch_size=%d, per GPU" % (args.rows, L, args.batch)
+    config = {"workload": workload, "rows_per_gpu": args.rows, "labels": L, "batch_size": args.batch, "seed": SEED,
+              "l2": "flushed (256 MiB write) between timed steps", "planted_matches": 100 + 50 * L}
+    from tests import synth
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cores = os.cpu_count() or 1
+        sample = cores * 6000
+        T = synth.make_table(max(sample, 4000), SEED, n_labels=L, n_base=20, n_per_label=2 if L else 0, batch_rows=args.batch)
+        for _ in range(max(args.warmup, 1)):
+            cpu_sample(T, min(sample, 1000), cores)
+        t = []
+        for _ in range(args.steps):
+            r, n, dt, flags = cpu_sample(T, sample, cores)
+            assert np.array_equal(np.nonzero(flags)[0], T["expected"][T["expected"] < n]), "oracle disagrees with planted matches"
+            t.append(dt)
+        ms = 1e3 * sum(t) / len(t)
+        value = sample / (ms / 1e3)
+        line = {"impl": "reference", "metric": "cudasp_scan rows/sec", "value": value, "unit": "rows/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port",
+                                 "sample": "%d rows of the same table per step, oracle/cudasp_oracle.c (bit-serial double-and-add "
+                                           "restatement of the reference algorithm), %d pthreads" % (sample, cores)},
+                "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "the reference's GPU code (gECC, sm_80-90 only) cannot be built here; this arm times the CPU restatement"}
+        print(json.dumps(line), flush=True)
+        return
+
+    # ------------------------------------------------------------------ our arm (GPU)
+    import torch
+    import cudasp_b200_loader
+    M = cudasp_b200_loader.load()
+    if not torch.cuda.is_available() or M.lib().cudasp_device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = local_rank
+    torch.cuda.set_device(dev)
+    T = synth.make_table(args.rows, SEED + rank, n_labels=L, n_base=100, n_per_label=50 if L else 0, batch_rows=args.batch)
+    rows = args.rows
+    q = M.Query(T["sk"], T["spend"], T["labels"], devices=[dev], batch_rows=args.batch,
+                max_outputs_per_batch=int(np.diff(T["offsets"][:: args.batch]).max(initial=0)) + 17 * args.batch)
+    batches = []
+    d_tw = torch.from_numpy(T["tweaks"]).cuda()
+    d_out = torch.from_numpy(T["outputs"]).cuda()
+    for base in range(0, rows, args.batch):
+        cnt = min(args.batch, rows - base)
+        o0 = int(T["offsets"][base])
+        off = (T["offsets"][base: base + cnt + 1] - o0).astype(np.int64)
+        batches.append(dict(base=base, cnt=cnt, tw=d_tw[base: base + cnt], out=d_out[o0:], off=torch.from_numpy(off).to(torch.int32).cuda(),
+                            ids=torch.zeros(cnt, dtype=torch.int32, device="cuda"), n=torch.zeros(1, dtype=torch.int32, device="cuda")))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    main_s = torch.cuda.current_stream()
+    side = [torch.cuda.Stream() for _ in range(max(args.streams, 1))]
+
+    def step_device():
+        start = torch.cuda.Event(enable_timing=True)
+        end = torch.cuda.Event(enable_timing=True)
+        start.record(main_s)
+        for s in side:
+            s.wait_event(start)
+        for i, b in enumerate(batches):
+            s = side[i % len(side)]
+            q.scan_device(dev, b["tw"].data_ptr(), b["out"].data_ptr(), b["off"].data_ptr(), b["cnt"], b["ids"].data_ptr(),
+                          b["n"].data_ptr(), s.cuda_stream)
+        for s in side:
+            e = torch.cuda.Event()
+            e.record(s)
+            main_s.wait_event(e)
+        end.record(main_s)
+        return start, end
+
+    def gathered_ids():
+        out = []
+        for b in batches:
+            n = int(b["n"].item())
+            out.extend((b["ids"][:n].to(torch.int64) + b["base"]).tolist())
+        return np.array(sorted(out), dtype=np.uint32)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+
+    for _ in range(args.warmup):
+        step_device()
+    torch.cuda.synchronize()
+    assert np.array_equal(gathered_ids(), T["expected"]), "GPU match set differs from the planted matches"
+    sampler = ClockSampler(dev)
+    sampler.start()
+    launches0 = q.launch_count()
+    barrier()
+    evs = []
+    for _ in range(args.steps):
+        flush.fill_(1)
+        evs.append(step_device())
+    barrier()
+    dev_ms = sum(s.elapsed_time(e) for s, e in evs) / args.steps
+    launches = q.launch_count() - launches0
+
+    # e2e: public host API, host buffers, copies inside the timed region
+    nb = len(batches)
+    h2d = rows * 64 + int(T["outputs"].shape[0]) * 8 + (rows + nb) * 4
+    d2h = sum((1 + min(b["cnt"], 1024)) * 4 for b in batches)
+    for _ in range(2):
+        ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
+    assert np.array_equal(ids, T["expected"]), "e2e match set differs from the planted matches"
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
+    torch.cuda.synchronize()
+    e2e_ms = 1e3 * (time.perf_counter() - t0) / args.steps
+    barrier()
+    clocks = sampler.finish()
+
+    # per-kernel times of one full batch (CUDA events on the launching stream, warm)
+    b0 = batches[0]
+    st = None
+    for _ in range(3):
+        st = M.profile_stages(q, dev, b0["tw"].data_ptr(), b0["out"].data_ptr(), b0["off"].data_ptr(), b0["cnt"], b0["ids"].data_ptr(),
+                              b0["n"].data_ptr())
+    if dist:
+        t = torch.tensor([dev_ms, e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank == 0:
+        peak, peak_src = measured_imad_peak()
+        value = world * rows / (dev_ms / 1e3)
+        e2e = world * rows / (e2e_ms / 1e3)
+        ladder_rate = b0["cnt"] * W32_LADDER / (st["ladder"] / 1e3)
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("k_ladder_dram_bytes_per_launch")
+        cores = os.cpu_count() or 1
+        cpu_rate, cpu_n, cpu_dt, _ = cpu_sample(T, min(rows, cores * 6000), cores)
+        line = {"metric": "cudasp_scan rows/sec", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u32", "data": "synthetic", "config": config, "clocks": clocks,
+                "e2e": {"value": e2e, "unit": "rows/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "api": "cudasp_scan_batch (C ABI, host buffers -> pinned staging -> async H2D -> kernels -> D2H ids)"},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "int-mul", "kernel": "k_ladder", "achieved": ladder_rate / 1e12, "peak": peak / 1e12,
+                             "unit": "T IMAD32 lane-ops/s", "frac": ladder_rate / peak, "traffic": traffic,
+                             "peak_source": peak_src, "algorithmic_ops_per_row": W32_LADDER, "rows_per_launch": b0["cnt"],
+                             "kernel_ms": st["ladder"], "stage_ms": st,
+                             "pipeline_frac_per_gpu": (value / world) * w32 / peak, "pipeline_ops_per_row": w32,
+                             "hbm_gbs_per_gpu": (value / world) * (64 + 8 * float(T["outputs"].shape[0]) / rows + 4) / 1e9},
+                "cpu_baseline": {"value": cpu_rate, "unit": "rows/s", "cores": cores, "kind": "port",
+                                 "sample": "%d rows of the same table, oracle/cudasp_oracle.c, %d pthreads, %.1f s" % (cpu_n, cores, cpu_dt)}}
+        print(json.dumps(line), flush=True)
+    q.close()
+    if dist:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -191,7 +191,11 @@ uint32_t inv_threads(uint32_t n) {
 // d_result: [0] = match count (reset here), [1..] = ids.  Either may be NULL (candidate mode).
 int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_tweaks, const int64_t *d_outputs,
                     const uint32_t *d_off, uint32_t rows, uint32_t *d_ids, uint32_t *d_count, cudaStream_t st,
-                    int64_t *d_cands, uint8_t *dbg_S, uint8_t *dbg_t, uint8_t *dbg_P0) {
+                    int64_t *d_cands, uint8_t *dbg_S, uint8_t *dbg_t, uint8_t *dbg_P0, cudaEvent_t *stage_evs = nullptr) {
+  // stage_evs (profiling entry only): 8 events recorded before each of the 7 possible kernels and
+  // after the last one; a stage that does not run records its event anyway (zero duration).
+  int ev_i = 0;
+  auto mark = [&]() { if (stage_evs) cudaEventRecord(stage_evs[ev_i++], st); };
   if (rows == 0) {
     if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
     return 0;
@@ -201,32 +205,44 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
   const host::QueryPlan &pl = q->plan;
   uint64_t nl = 0;
   if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
+  mark();
   if (!pl.fp.zero_scalar) {
     const uint32_t grid = (rows + LADDER_BLOCK - 1) / LADDER_BLOCK;
     k_ladder<LADDER_BLOCK, LADDER_MINB><<<grid, LADDER_BLOCK, LADDER_SMEM_WORDS_PER_THREAD * 4 * LADDER_BLOCK, st>>>(
         d_tweaks, w.X, w.Y, w.Z, rows, pl.lp);
+    mark();
     const uint32_t T = inv_threads(rows);
     k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
     nl += 2;
+  } else {
+    mark();
   }
+  mark();
   {
     const uint32_t grid = (rows + HASH_BLOCK - 1) / HASH_BLOCK;
     k_hash_fixedbase<HASH_BLOCK, HASH_MINB><<<grid, HASH_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, dc.d_gtab, pl.fp, dbg_S, dbg_t);
+    mark();
     const uint32_t T = inv_threads(rows);
     k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
+    mark();
     const uint32_t fgrid = (rows + FINAL_BLOCK - 1) / FINAL_BLOCK;
     k_final_base<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, d_outputs, d_off, dc.d_labels, L, w.D, w.flags,
                                                             d_ids, d_count, d_cands, dbg_P0);
     nl += 3;
+    mark();
     if (L) {
       const uint64_t n64 = (uint64_t)rows * L;
       if (n64 > 0xffffffffull) return fail(q, CUDASP_ERR_ARG, "rows * labels exceeds 2^32");
       const uint32_t n = (uint32_t)n64, T2 = inv_threads(n);
       k_batch_inv<<<(T2 + 127) / 128, 128, 0, st>>>(w.D, w.DS, n, T2);
+      mark();
       k_final_labels<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.D, rows, d_outputs, d_off, dc.d_labels, L, w.flags,
                                                                 d_ids, d_count, d_cands);
       nl += 2;
+    } else {
+      mark();
     }
+    mark();
   }
   CU(q, cudaGetLastError());
   q->launches += nl;
@@ -571,6 +587,33 @@ int cudasp_scan_device(cudasp_query *q, int device, const uint8_t *d_tweak_keys,
   if (rc) return rc;
   CU(q, cudaEventRecord(w->free_evt, st));
   return CUDASP_OK;
+}
+
+// ---- per-stage timing (bench.py roofline) -----------------------------------------------
+int cudasp_profile_stages(cudasp_query *q, int device, const uint8_t *d_tweak_keys, const int64_t *d_outputs,
+                          const uint32_t *d_out_offsets, uint32_t rows, uint32_t *d_match_ids, uint32_t *d_n_matches,
+                          float *stage_ms) {
+  if (!q || !stage_ms) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  DevCtx *dc = nullptr;
+  for (DevCtx &d : q->devs) if (d.device == device) dc = &d;
+  if (!dc) return fail(q, CUDASP_ERR_ARG, "device is not part of this query");
+  if (rows == 0 || rows > q->batch_rows) return fail(q, CUDASP_ERR_ARG, "rows out of range");
+  CU(q, cudaSetDevice(device));
+  cudaEvent_t ev[8];
+  for (int i = 0; i < 8; i++) CU(q, cudaEventCreate(&ev[i]));
+  Workspace &w = dc->slots[0]->ws;
+  cudaStream_t st = dc->own_stream;
+  CU(q, cudaStreamWaitEvent(st, w.free_evt, 0));
+  int rc = launch_pipeline(q, *dc, w, d_tweak_keys, d_outputs, d_out_offsets, rows, d_match_ids, d_n_matches, st, nullptr, nullptr,
+                           nullptr, nullptr, ev);
+  if (!rc) {
+    cudaEventRecord(w.free_evt, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) rc = fail(q, CUDASP_ERR_CUDA, cudaGetErrorString(e));
+    for (int i = 0; i < 7 && !rc; i++) cudaEventElapsedTime(&stage_ms[i], ev[i], ev[i + 1]);
+  }
+  for (int i = 0; i < 8; i++) cudaEventDestroy(ev[i]);
+  return rc;
 }
 
 // ---- introspection --------------------------------------------------------------------

@@ -32,7 +32,7 @@ class Result(C.Structure):
 
 EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "cudasp_query_destroy", "cudasp_scan_batch",
            "cudasp_acquire_slot", "cudasp_submit_slot", "cudasp_poll", "cudasp_wait", "cudasp_release_result",
-           "cudasp_scan_device", "cudasp_scan_candidates", "cudasp_scan_intermediates", "cudasp_test_field",
+           "cudasp_scan_device", "cudasp_profile_stages", "cudasp_scan_candidates", "cudasp_scan_intermediates", "cudasp_test_field",
            "cudasp_launch_count", "cudasp_query_info", "cudasp_version"]
 
 
@@ -57,6 +57,7 @@ def lib():
         L.cudasp_wait.argtypes = [vp, C.POINTER(Result)]
         L.cudasp_release_result.argtypes = [vp, C.POINTER(Result)]
         L.cudasp_scan_device.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, vp, vp]
+        L.cudasp_profile_stages.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, vp, C.POINTER(C.c_float)]
         L.cudasp_scan_candidates.argtypes = [vp, vp, C.c_uint32, vp]
         L.cudasp_scan_intermediates.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
         L.cudasp_test_field.argtypes = [C.c_int, C.c_int, vp, vp, vp, C.c_uint32]
@@ -162,6 +163,15 @@ class Query:
     def scan_device(self, device: int, d_tweaks: int, d_outputs: int, d_offsets: int, rows: int, d_ids: int, d_count: int, stream: int = 0):
         """Raw device pointers (ints), e.g. torch tensor .data_ptr(); asynchronous on `stream`."""
         self._check(lib().cudasp_scan_device(self._h, device, d_tweaks, d_outputs, d_offsets, rows, d_ids, d_count, stream))
+
+
+STAGES = ["ladder", "inv_z1", "hash_fixedbase", "inv_z2", "final_base", "inv_labels", "final_labels"]
+
+
+def profile_stages(q: "Query", device: int, d_tweaks: int, d_outputs: int, d_offsets: int, rows: int, d_ids: int, d_count: int):
+    ms = (C.c_float * 7)()
+    q._check(lib().cudasp_profile_stages(q._h, device, d_tweaks, d_outputs, d_offsets, rows, d_ids, d_count, ms))
+    return dict(zip(STAGES, [float(x) for x in ms]))
 
 
 def test_field(op: int, a: Sequence[int], b: Sequence[int], device: int = 0):

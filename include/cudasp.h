@@ -111,6 +111,13 @@ int cudasp_scan_device(cudasp_query *q, int device, const uint8_t *d_tweak_keys,
                        const uint32_t *d_out_offsets, uint32_t rows, uint32_t *d_match_ids,
                        uint32_t *d_n_matches, void *stream);
 
+/* Synchronous variant of cudasp_scan_device that times each kernel with CUDA events on the query's
+ * own stream: stage_ms[7] = ladder, inv(Z1), hash+fixed-base, inv(Z2), base, inv(labels), labels
+ * (stages that do not run report 0).  Used by bench.py for the per-kernel roofline. */
+int cudasp_profile_stages(cudasp_query *q, int device, const uint8_t *d_tweak_keys, const int64_t *d_outputs,
+                          const uint32_t *d_out_offsets, uint32_t rows, uint32_t *d_match_ids, uint32_t *d_n_matches,
+                          float *stage_ms);
+
 /* ---- introspection used by the parity tests and bench.py -----------------------------------
  * Per-row candidates instead of match flags: cands[r*(1+L) + 0] = base, [.. + 1 + i] = label i. */
 int cudasp_scan_candidates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands);
