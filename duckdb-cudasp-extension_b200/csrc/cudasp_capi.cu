@@ -26,7 +26,7 @@ namespace {
 
 thread_local std::string tl_err;
 
-const int SLOTS_PER_DEVICE = 3;
+const int SLOTS_PER_DEVICE = 3, MAX_SLOTS_PER_DEVICE = 64;
 const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
 const int LADDER_BLOCK = 128, LADDER_MINB = 3;
 const int HASH_BLOCK = 128, HASH_MINB = 3;
@@ -282,6 +282,15 @@ void cudasp_query_destroy(cudasp_query *q) {
 int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64], const uint8_t *label_keys,
                         uint32_t n_labels, const int *devices, int n_devices, uint32_t batch_rows,
                         uint64_t max_outputs_per_batch, cudasp_query **out) {
+  return cudasp_query_create_ex(scan_private_key, spend_public_key, label_keys, n_labels, devices, n_devices, batch_rows,
+                                max_outputs_per_batch, 0, out);
+}
+
+int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64], const uint8_t *label_keys,
+                           uint32_t n_labels, const int *devices, int n_devices, uint32_t batch_rows,
+                           uint64_t max_outputs_per_batch, uint32_t slots_per_device, cudasp_query **out) {
+  if (slots_per_device == 0) slots_per_device = SLOTS_PER_DEVICE;
+  if (slots_per_device > (uint32_t)MAX_SLOTS_PER_DEVICE) return fail(nullptr, CUDASP_ERR_ARG, "slots_per_device out of range");
   if (!out) return fail(nullptr, CUDASP_ERR_ARG, "out is NULL");
   *out = nullptr;
   if (!scan_private_key || !spend_public_key) return fail(nullptr, CUDASP_ERR_ARG, "key pointer is NULL");
@@ -320,7 +329,7 @@ int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_
       if (e == cudaSuccess) e = cudaMemcpy(dc.d_labels, q->plan.labels.data(), n_labels * sizeof(ge), cudaMemcpyHostToDevice);
     }
     if (e != cudaSuccess) { cudasp_query_destroy(q); return fail(nullptr, CUDASP_ERR_CUDA, cudaGetErrorString(e)); }
-    for (int k = 0; k < SLOTS_PER_DEVICE; k++) {
+    for (uint32_t k = 0; k < slots_per_device; k++) {
       Slot *s = new Slot();
       s->id = slot_id++;
       s->dev_index = (int)i;
@@ -438,6 +447,24 @@ int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
   slot->cap_rows = s->cap_rows;
   slot->cap_outputs = s->cap_outputs;
   return CUDASP_OK;
+}
+
+int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
+  if (!q || !slot) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  Slot *s;
+  {
+    std::lock_guard<std::mutex> lk(q->mu);
+    s = try_acquire_locked(q);
+  }
+  if (!s) return 0;
+  slot->slot_id = s->id;
+  slot->device = q->devs[s->dev_index].device;
+  slot->tweak_keys = s->h_tweaks;
+  slot->outputs = s->h_outputs;
+  slot->out_offsets = s->h_off;
+  slot->cap_rows = s->cap_rows;
+  slot->cap_outputs = s->cap_outputs;
+  return 1;
 }
 
 int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag) {

@@ -1,0 +1,474 @@
+// cudasp_extension.cpp -- the DuckDB side of the drop-in: table function `cudasp_scan` over the C ABI.
+//
+// Plain C++ (no nvcc): everything GPU-related lives behind include/cudasp.h (libcudasp_b200.so).
+// Same extension name (`cudasp`), entry point (`cudasp_duckdb_cpp_init`), function name, positional and
+// named parameters, input columns, output schema, argument checks and error texts as the reference's
+// src/cudasp_extension.cu (bind :420-509, states :87-152, accumulate :154-224, in-out protocol :534-624,
+// registration :626-659).  What differs is the data path: rows are written straight from the DuckDB
+// vectors into a pinned staging slot of the C ABI (no per-row std::string, no limb conversion, no
+// transposition), a full slot is submitted asynchronously, and results (row ids) are collected whenever a
+// worker has nothing better to do.  GPU errors THROW (the reference printf()s and drops the batch, :325,378).
+#include "cudasp_extension.hpp"
+
+#include "duckdb.hpp"
+#include "duckdb/common/exception.hpp"
+#include "duckdb/function/table_function.hpp"
+#include "duckdb/main/extension/extension_loader.hpp"
+#include "duckdb/parallel/task_scheduler.hpp"
+
+#include <atomic>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+
+#include "../../include/cudasp.h"
+
+namespace duckdb {
+
+namespace {
+
+constexpr idx_t SCALAR_SIZE = 32;      // scan_private_key: 32 B little-endian
+constexpr idx_t POINT_SIZE = 64;       // x_LE || y_LE
+constexpr idx_t DEFAULT_BATCH = 300000;  // reference default (:473)
+constexpr idx_t MAX_BATCH = 10000000;
+
+struct CudaspScanBindData : public TableFunctionData {
+	string scan_private_key;
+	string spend_public_key;
+	string label_keys;  // n_labels * 64 B, concatenated
+	uint32_t n_labels = 0;
+	idx_t batch_size = DEFAULT_BATCH;
+};
+
+// Host-side columns of one submitted batch that never go to the GPU: only needed for matched rows.
+struct InFlightBatch {
+	vector<char> txid_bytes;
+	vector<uint32_t> txid_end;   // txid i = txid_bytes[txid_end[i-1] .. txid_end[i])
+	vector<int32_t> heights;
+	const uint8_t *tweak_keys = nullptr;  // the slot's pinned buffer: valid until the result is released
+};
+
+struct CudaspScanState : public GlobalTableFunctionState {
+	~CudaspScanState() override {
+		if (query) {
+			cudasp_query_destroy(query);
+		}
+	}
+	idx_t MaxThreads() const override {
+		return GlobalTableFunctionState::MAX_THREADS;
+	}
+
+	cudasp_query *query = nullptr;
+	std::atomic<uint64_t> next_tag {1};
+	std::mutex inflight_lock;
+	std::unordered_map<uint64_t, unique_ptr<InFlightBatch>> inflight;
+
+	// protocol state, as in the reference: nothing is emitted before every worker has finalized (:554-591)
+	std::atomic<uint64_t> currently_adding {0};
+	std::mutex finalize_lock;
+	std::atomic<bool> output_thread_claimed {false};
+
+	std::mutex output_lock;
+	vector<string> output_txids;
+	vector<int32_t> output_heights;
+	vector<string> output_tweak_keys;
+	idx_t output_position = 0;
+};
+
+struct CudaspScanLocalState : public LocalTableFunctionState {
+	bool finalized = false;
+	bool is_output_thread = false;
+	bool have_slot = false;
+	cudasp_slot slot;
+	uint32_t rows = 0;
+	uint64_t n_outputs = 0;
+	unique_ptr<InFlightBatch> meta;
+};
+
+[[noreturn]] void ThrowGpu(CudaspScanState &state, const char *what) {
+	const char *msg = cudasp_last_error(state.query);
+	throw IOException("cudasp_scan: %s failed: %s", what, msg ? msg : "unknown error");
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------ bind
+// Same checks, same order, same messages as the reference's CudaspScanBind (:420-509).
+static unique_ptr<FunctionData> CudaspScanBind(ClientContext &context, TableFunctionBindInput &input,
+                                               vector<LogicalType> &return_types, vector<string> &names) {
+	if (input.inputs.size() != 4) {
+		throw InvalidInputException("cudasp_scan requires 4 arguments: TABLE, scan_private_key BLOB, spend_public_key "
+		                            "BLOB, and label_keys LIST[BLOB]");
+	}
+	auto result = make_uniq<CudaspScanBindData>();
+
+	auto &sk = input.inputs[1];
+	if (sk.type().id() != LogicalTypeId::BLOB) {
+		throw InvalidInputException("Second argument must be a BLOB (32-byte scan_private_key)");
+	}
+	result->scan_private_key = StringValue::Get(sk);
+	if (result->scan_private_key.size() != SCALAR_SIZE) {
+		throw InvalidInputException("scan_private_key must be exactly 32 bytes, got %llu bytes",
+		                            (uint64_t)result->scan_private_key.size());
+	}
+
+	auto &spend = input.inputs[2];
+	if (spend.type().id() != LogicalTypeId::BLOB) {
+		throw InvalidInputException("Third argument must be a BLOB (64-byte spend_public_key)");
+	}
+	result->spend_public_key = StringValue::Get(spend);
+	if (result->spend_public_key.size() != POINT_SIZE) {
+		throw InvalidInputException("spend_public_key must be exactly 64 bytes, got %llu bytes",
+		                            (uint64_t)result->spend_public_key.size());
+	}
+
+	auto &labels = input.inputs[3];
+	if (labels.type().id() != LogicalTypeId::LIST) {
+		throw InvalidInputException("Fourth argument must be a LIST[BLOB] (label keys)");
+	}
+	if (!labels.IsNull()) {
+		for (auto &child : ListValue::GetChildren(labels)) {
+			if (child.type().id() != LogicalTypeId::BLOB) {
+				throw InvalidInputException("All elements in label_keys must be BLOBs");
+			}
+			const string &key = StringValue::Get(child);
+			if (key.size() != POINT_SIZE) {
+				throw InvalidInputException("Each label key must be exactly 64 bytes, got %llu bytes", (uint64_t)key.size());
+			}
+			result->label_keys += key;
+			result->n_labels++;
+		}
+	}
+	if (result->n_labels > CUDASP_MAX_LABELS) {
+		throw InvalidInputException("cudasp_scan supports at most %llu label keys", (uint64_t)CUDASP_MAX_LABELS);
+	}
+
+	auto bs = input.named_parameters.find("batch_size");
+	if (bs != input.named_parameters.end()) {
+		auto tid = bs->second.type().id();
+		if (tid != LogicalTypeId::INTEGER && tid != LogicalTypeId::BIGINT) {
+			throw InvalidInputException("batch_size parameter must be an INTEGER");
+		}
+		int64_t v = bs->second.GetValue<int64_t>();
+		if (v <= 0) {
+			throw InvalidInputException("batch_size must be positive, got %lld", (long long)v);
+		}
+		if (v > (int64_t)MAX_BATCH) {
+			throw InvalidInputException("batch_size too large (max 10,000,000), got %lld", (long long)v);
+		}
+		result->batch_size = (idx_t)v;
+	}
+
+	return_types = {LogicalType::BLOB, LogicalType::INTEGER, LogicalType::BLOB};
+	names = {"txid", "height", "tweak_key"};
+	return std::move(result);
+}
+
+// ------------------------------------------------------------------------------------------ init
+// Global init does the once-per-query work the reference repeats per batch (key conversion, :277-297) and per
+// process (Solver::initialize, gsv.h:1094-1122): cudasp_query_create recodes the scan key, uploads tables,
+// allocates pinned staging + device buffers on every visible GPU.
+static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &context, TableFunctionInitInput &input) {
+	auto &bind = input.bind_data->Cast<CudaspScanBindData>();
+	auto state = make_uniq<CudaspScanState>();
+	int n_dev = cudasp_device_count();
+	if (n_dev <= 0) {
+		throw IOException("cudasp_scan: no CUDA device available (%s)", cudasp_last_error(nullptr));
+	}
+	idx_t threads = MaxValue<idx_t>(1, NumericCast<idx_t>(TaskScheduler::GetScheduler(context).NumberOfThreads()));
+	// every worker can hold one slot while filling it; two more per device keep a copy and a batch in flight
+	uint32_t slots = (uint32_t)MinValue<idx_t>(64, (threads + n_dev - 1) / n_dev + 2);
+	// cap the pinned/device footprint for very large batch sizes (~200 B of staging per row and slot)
+	while (slots > 3 && (uint64_t)slots * bind.batch_size > 48000000ull) {
+		slots--;
+	}
+	int rc = cudasp_query_create_ex(const_data_ptr_cast(bind.scan_private_key.data()),
+	                                const_data_ptr_cast(bind.spend_public_key.data()),
+	                                bind.n_labels ? const_data_ptr_cast(bind.label_keys.data()) : nullptr, bind.n_labels,
+	                                nullptr, 0, (uint32_t)bind.batch_size, 0, slots, &state->query);
+	if (rc != CUDASP_OK) {
+		const char *msg = cudasp_last_error(nullptr);
+		if (rc == CUDASP_ERR_KEY || rc == CUDASP_ERR_ARG) {
+			throw InvalidInputException("cudasp_scan: %s", msg ? msg : "invalid keys");
+		}
+		throw IOException("cudasp_scan: GPU initialisation failed: %s", msg ? msg : "unknown error");
+	}
+	return std::move(state);
+}
+
+static unique_ptr<LocalTableFunctionState> CudaspScanLocalInit(ExecutionContext &context, TableFunctionInitInput &input,
+                                                               GlobalTableFunctionState *global_state) {
+	auto &state = global_state->Cast<CudaspScanState>();
+	state.currently_adding++;
+	return make_uniq<CudaspScanLocalState>();
+}
+
+// ------------------------------------------------------------------------------------------ results
+// Copy the matched rows of one finished batch into the global result vectors, then recycle its slot.
+// Replaces the O(batch) scan of managed match flags under the output mutex (:383-391).
+static void CollectResult(CudaspScanState &state, const cudasp_result &r) {
+	unique_ptr<InFlightBatch> meta;
+	{
+		std::lock_guard<std::mutex> guard(state.inflight_lock);
+		auto it = state.inflight.find(r.tag);
+		if (it == state.inflight.end()) {
+			throw InternalException("cudasp_scan: result for an unknown batch tag");
+		}
+		meta = std::move(it->second);
+		state.inflight.erase(it);
+	}
+	if (r.n_matches) {
+		std::lock_guard<std::mutex> guard(state.output_lock);
+		for (uint32_t k = 0; k < r.n_matches; k++) {
+			const uint32_t i = r.match_ids[k];
+			const uint32_t b = i ? meta->txid_end[i - 1] : 0, e = meta->txid_end[i];
+			state.output_txids.emplace_back(meta->txid_bytes.data() + b, e - b);
+			state.output_heights.push_back(meta->heights[i]);
+			state.output_tweak_keys.emplace_back(const_char_ptr_cast(meta->tweak_keys) + (size_t)i * POINT_SIZE, POINT_SIZE);
+		}
+	}
+	if (cudasp_release_result(state.query, &r) != CUDASP_OK) {
+		ThrowGpu(state, "cudasp_release_result");
+	}
+}
+
+// Collect every batch that has already finished (block == false) or every batch in flight (block == true).
+static void Drain(CudaspScanState &state, bool block) {
+	cudasp_result r;
+	for (;;) {
+		int rc = block ? cudasp_wait(state.query, &r) : cudasp_poll(state.query, &r);
+		if (rc < 0) {
+			ThrowGpu(state, block ? "cudasp_wait" : "cudasp_poll");
+		}
+		if (rc == 0) {
+			return;
+		}
+		CollectResult(state, r);
+	}
+}
+
+static void EnsureSlot(CudaspScanState &state, CudaspScanLocalState &local) {
+	if (local.have_slot) {
+		return;
+	}
+	for (;;) {
+		int rc = cudasp_try_acquire_slot(state.query, &local.slot);
+		if (rc < 0) {
+			ThrowGpu(state, "cudasp_try_acquire_slot");
+		}
+		if (rc == 1) {
+			break;
+		}
+		// every slot is busy: help by collecting the oldest batch in flight (this frees a slot); if nothing is in
+		// flight the slots are all being filled by other workers -- block until one of them is recycled.
+		cudasp_result r;
+		rc = cudasp_wait(state.query, &r);
+		if (rc < 0) {
+			ThrowGpu(state, "cudasp_wait");
+		}
+		if (rc == 1) {
+			CollectResult(state, r);
+		} else {
+			if (cudasp_acquire_slot(state.query, &local.slot) != CUDASP_OK) {
+				ThrowGpu(state, "cudasp_acquire_slot");
+			}
+			break;
+		}
+	}
+	local.have_slot = true;
+	local.rows = 0;
+	local.n_outputs = 0;
+	local.slot.out_offsets[0] = 0;
+	local.meta = make_uniq<InFlightBatch>();
+	local.meta->tweak_keys = local.slot.tweak_keys;
+}
+
+// Hand the filled part of the slot to the GPU (async H2D + kernels + D2H on the slot's stream).  Replaces ProcessBatch
+// (:226-410): no marshalling is left to do, the slot already holds the device layout.
+static void SubmitSlot(CudaspScanState &state, CudaspScanLocalState &local) {
+	if (!local.have_slot || local.rows == 0) {
+		return;
+	}
+	const uint64_t tag = state.next_tag++;
+	{
+		std::lock_guard<std::mutex> guard(state.inflight_lock);
+		state.inflight[tag] = std::move(local.meta);
+	}
+	if (cudasp_submit_slot(state.query, &local.slot, local.rows, local.n_outputs, tag) != CUDASP_OK) {
+		ThrowGpu(state, "cudasp_submit_slot");
+	}
+	local.have_slot = false;
+	local.rows = 0;
+	local.n_outputs = 0;
+}
+
+// ------------------------------------------------------------------------------------------ execute
+// One DataChunk (<= 2048 rows) -> pinned staging.  Row rules are the reference's AccumulateInput (:154-224):
+// a row with NULL txid, height or tweak_key is dropped; a NULL outputs list is an empty list; NULL list children
+// are skipped.  A tweak_key that is not 64 bytes can never match (the reference reads out of bounds): dropped.
+static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local, const CudaspScanBindData &bind,
+                            DataChunk &input) {
+	if (input.ColumnCount() < 4) {
+		throw InvalidInputException("cudasp_scan input must have 4 columns: txid, height, tweak_key, outputs");
+	}
+	auto &out_type = input.data[3].GetType();
+	if (input.data[0].GetType().InternalType() != PhysicalType::VARCHAR || input.data[1].GetType().id() != LogicalTypeId::INTEGER ||
+	    input.data[2].GetType().InternalType() != PhysicalType::VARCHAR || out_type.id() != LogicalTypeId::LIST ||
+	    ListType::GetChildType(out_type).id() != LogicalTypeId::BIGINT) {
+		throw InvalidInputException("cudasp_scan input columns must be (txid BLOB, height INTEGER, tweak_key BLOB, outputs BIGINT[])");
+	}
+	const idx_t count = input.size();
+	UnifiedVectorFormat txid_f, height_f, tweak_f, list_f, child_f;
+	input.data[0].ToUnifiedFormat(count, txid_f);
+	input.data[1].ToUnifiedFormat(count, height_f);
+	input.data[2].ToUnifiedFormat(count, tweak_f);
+	input.data[3].ToUnifiedFormat(count, list_f);
+	auto &child = ListVector::GetEntry(input.data[3]);
+	child.ToUnifiedFormat(ListVector::GetListSize(input.data[3]), child_f);
+	auto txids = UnifiedVectorFormat::GetData<string_t>(txid_f);
+	auto heights = UnifiedVectorFormat::GetData<int32_t>(height_f);
+	auto tweaks = UnifiedVectorFormat::GetData<string_t>(tweak_f);
+	auto lists = UnifiedVectorFormat::GetData<list_entry_t>(list_f);
+	auto values = UnifiedVectorFormat::GetData<int64_t>(child_f);
+
+	for (idx_t r = 0; r < count; r++) {
+		const idx_t ti = txid_f.sel->get_index(r), hi = height_f.sel->get_index(r), wi = tweak_f.sel->get_index(r);
+		if (!txid_f.validity.RowIsValid(ti) || !height_f.validity.RowIsValid(hi) || !tweak_f.validity.RowIsValid(wi)) {
+			continue;
+		}
+		const string_t &tw = tweaks[wi];
+		if (tw.GetSize() != POINT_SIZE) {
+			continue;
+		}
+		const idx_t li = list_f.sel->get_index(r);
+		const bool has_list = list_f.validity.RowIsValid(li);
+		const idx_t list_len = has_list ? lists[li].length : 0;
+		EnsureSlot(state, local);
+		// cut the batch early if this row's outputs would overflow the slot's output capacity
+		if (local.rows && local.n_outputs + list_len > local.slot.cap_outputs) {
+			SubmitSlot(state, local);
+			EnsureSlot(state, local);
+		}
+		if (list_len > local.slot.cap_outputs) {
+			throw InvalidInputException("cudasp_scan: a row has %llu outputs, more than a batch can hold (%llu)",
+			                            (uint64_t)list_len, (uint64_t)local.slot.cap_outputs);
+		}
+		const uint32_t row = local.rows;
+		memcpy(local.slot.tweak_keys + (size_t)row * POINT_SIZE, tw.GetData(), POINT_SIZE);
+		uint64_t n_out = local.n_outputs;
+		if (has_list) {
+			const idx_t off = lists[li].offset;
+			for (idx_t j = 0; j < list_len; j++) {
+				const idx_t ci = child_f.sel->get_index(off + j);
+				if (child_f.validity.RowIsValid(ci)) {
+					local.slot.outputs[n_out++] = values[ci];
+				}
+			}
+		}
+		local.n_outputs = n_out;
+		local.slot.out_offsets[row + 1] = (uint32_t)n_out;
+		auto &meta = *local.meta;
+		const string_t &tx = txids[ti];
+		meta.txid_bytes.insert(meta.txid_bytes.end(), tx.GetData(), tx.GetData() + tx.GetSize());
+		meta.txid_end.push_back((uint32_t)meta.txid_bytes.size());
+		meta.heights.push_back(heights[hi]);
+		local.rows = row + 1;
+		if (local.rows >= bind.batch_size || local.rows >= local.slot.cap_rows) {
+			SubmitSlot(state, local);
+		}
+	}
+}
+
+// Never emits during Execute (same protocol as the reference, :534-552); finished batches are collected
+// opportunistically so that slots recycle while the scan is still feeding rows.
+static OperatorResultType CudaspScanFunction(ExecutionContext &context, TableFunctionInput &data_p, DataChunk &input,
+                                             DataChunk &output) {
+	auto &bind = data_p.bind_data->Cast<CudaspScanBindData>();
+	auto &state = data_p.global_state->Cast<CudaspScanState>();
+	auto &local = data_p.local_state->Cast<CudaspScanLocalState>();
+	if (input.size() > 0) {
+		AccumulateInput(state, local, bind, input);
+		Drain(state, false);
+	}
+	return OperatorResultType::NEED_MORE_INPUT;
+}
+
+// ------------------------------------------------------------------------------------------ finalize
+// Same protocol as the reference's CudaspScanFinalFunction (:554-624): every worker flushes its partial batch; the
+// LAST worker to finalize claims the output role, waits for everything in flight and streams the global result out
+// STANDARD_VECTOR_SIZE rows at a time.  (One emitting thread keeps DuckDB's batch-index bookkeeping happy, :580-589.)
+static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &context, TableFunctionInput &data_p,
+                                                          DataChunk &output) {
+	auto &state = data_p.global_state->Cast<CudaspScanState>();
+	auto &local = data_p.local_state->Cast<CudaspScanLocalState>();
+
+	if (!local.finalized) {
+		SubmitSlot(state, local);
+		Drain(state, false);
+		std::lock_guard<std::mutex> guard(state.finalize_lock);
+		state.currently_adding--;
+		local.finalized = true;
+	}
+	if (!local.is_output_thread) {
+		if (state.currently_adding != 0) {
+			return OperatorFinalizeResultType::FINISHED;
+		}
+		bool expected = false;
+		if (!state.output_thread_claimed.compare_exchange_strong(expected, true)) {
+			return OperatorFinalizeResultType::FINISHED;
+		}
+		local.is_output_thread = true;
+		Drain(state, true);  // barrier: every submitted batch has been collected after this
+	}
+
+	const idx_t remaining = state.output_txids.size() - state.output_position;
+	const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, remaining);
+	if (n > 0) {
+		auto txid_out = FlatVector::GetData<string_t>(output.data[0]);
+		auto height_out = FlatVector::GetData<int32_t>(output.data[1]);
+		auto tweak_out = FlatVector::GetData<string_t>(output.data[2]);
+		for (idx_t i = 0; i < n; i++) {
+			const idx_t src = state.output_position + i;
+			txid_out[i] = StringVector::AddStringOrBlob(output.data[0], state.output_txids[src]);
+			height_out[i] = state.output_heights[src];
+			tweak_out[i] = StringVector::AddStringOrBlob(output.data[2], state.output_tweak_keys[src]);
+		}
+		output.SetCardinality(n);
+		state.output_position += n;
+	}
+	return state.output_position < state.output_txids.size() ? OperatorFinalizeResultType::HAVE_MORE_OUTPUT
+	                                                         : OperatorFinalizeResultType::FINISHED;
+}
+
+// ------------------------------------------------------------------------------------------ registration
+static void LoadInternal(ExtensionLoader &loader) {
+	TableFunction func("cudasp_scan",
+	                   {LogicalType::TABLE, LogicalType::BLOB, LogicalType::BLOB, LogicalType::LIST(LogicalType::BLOB)}, nullptr,
+	                   CudaspScanBind, CudaspScanInit, CudaspScanLocalInit);
+	func.in_out_function = CudaspScanFunction;
+	func.in_out_function_final = CudaspScanFinalFunction;
+	func.named_parameters["batch_size"] = LogicalType::INTEGER;
+	loader.RegisterFunction(func);
+}
+
+void CudaspExtension::Load(ExtensionLoader &loader) {
+	LoadInternal(loader);
+}
+std::string CudaspExtension::Name() {
+	return "cudasp";
+}
+std::string CudaspExtension::Version() const {
+#ifdef EXT_VERSION_CUDASP
+	return EXT_VERSION_CUDASP;
+#else
+	return cudasp_version();
+#endif
+}
+
+}  // namespace duckdb
+
+extern "C" {
+DUCKDB_CPP_EXTENSION_ENTRY(cudasp, loader) {
+	duckdb::LoadInternal(loader);
+}
+}

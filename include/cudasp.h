@@ -59,6 +59,14 @@ int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_
                         const int *devices, int n_devices, uint32_t batch_rows,
                         uint64_t max_outputs_per_batch, cudasp_query **out);
 
+/* Same, with the number of staging slots per device chosen by the caller (0 = default 3; max 64).
+ * A host with T producer threads (DuckDB workers, src/cudasp_extension.cu:516-532) wants about
+ * T / n_devices + 2 so that no producer waits for a slot while batches are in flight. */
+int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64],
+                           const uint8_t *label_keys, uint32_t n_labels, const int *devices, int n_devices,
+                           uint32_t batch_rows, uint64_t max_outputs_per_batch, uint32_t slots_per_device,
+                           cudasp_query **out);
+
 /* Replaces FreeBatchScanState (src/cudasp_gpu.cu:969-1023).  Waits for in-flight batches. */
 void cudasp_query_destroy(cudasp_query *q);
 
@@ -94,6 +102,8 @@ typedef struct cudasp_result {
 
 /* Blocks until a staging slot is free (a slot is recycled by cudasp_release_result). */
 int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot);
+/* Non-blocking variant: returns 1 and fills *slot, or 0 when every slot is busy. */
+int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot);
 /* Enqueue H2D + kernels + D2H for `rows` rows / `n_outputs` outputs of an acquired slot. */
 int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag);
 /* Returns 1 and fills *r when a finished batch is available, 0 when none is finished yet. */
