@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <atomic>
 #include <condition_variable>
 #include <deque>
@@ -187,6 +188,37 @@ uint32_t inv_threads(uint32_t n) {
   return std::max<uint32_t>(std::min<uint32_t>(t, n), 1u);
 }
 
+// K1 launch shapes.  Variant 0 is the production default; the others exist for tuning and are selected
+// with the environment variable CUDASP_LADDER_VARIANT (read once per process).
+template <int BLOCK, int MINB, int SYNC>
+void launch_ladder_t(const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp, cudaStream_t st) {
+  static std::once_flag once;
+  const int smem = LADDER_SMEM_WORDS_PER_THREAD * 4 * BLOCK;
+  std::call_once(once, [&] {
+    cudaFuncSetAttribute(k_ladder<BLOCK, MINB, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  });
+  const uint32_t grid = (rows + BLOCK - 1) / BLOCK;
+  k_ladder<BLOCK, MINB, SYNC><<<grid, BLOCK, smem, st>>>(d_tweaks, X, Y, Z, rows, lp);
+}
+int ladder_variant() {
+  static int v = [] { const char *e = getenv("CUDASP_LADDER_VARIANT"); return e ? atoi(e) : 0; }();
+  return v;
+}
+void launch_ladder(int variant, const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp,
+                   cudaStream_t st) {
+  switch (variant) {
+    default:
+    case 0: launch_ladder_t<128, 4, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;   // best measured (profiles/r01c)
+    case 1: launch_ladder_t<128, 3, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 2: launch_ladder_t<128, 4, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 3: launch_ladder_t<128, 3, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 4: launch_ladder_t<384, 1, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 5: launch_ladder_t<512, 1, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 6: launch_ladder_t<256, 2, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 7: launch_ladder_t<512, 1, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
+  }
+}
+
 // Enqueue the whole per-batch pipeline on `st`.  All pointers are device pointers.
 // d_result: [0] = match count (reset here), [1..] = ids.  Either may be NULL (candidate mode).
 int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_tweaks, const int64_t *d_outputs,
@@ -207,9 +239,7 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
   if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
   mark();
   if (!pl.fp.zero_scalar) {
-    const uint32_t grid = (rows + LADDER_BLOCK - 1) / LADDER_BLOCK;
-    k_ladder<LADDER_BLOCK, LADDER_MINB><<<grid, LADDER_BLOCK, LADDER_SMEM_WORDS_PER_THREAD * 4 * LADDER_BLOCK, st>>>(
-        d_tweaks, w.X, w.Y, w.Z, rows, pl.lp);
+    launch_ladder(ladder_variant(), d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, st);
     mark();
     const uint32_t T = inv_threads(rows);
     k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);

@@ -20,8 +20,10 @@
 #if defined(__CUDACC__)
 #define CSP_HD __host__ __device__ __forceinline__
 #define CSP_D __device__ __forceinline__
+#define CSP_CE __host__ __device__ constexpr
 #else
 #define CSP_HD inline
+#define CSP_CE constexpr
 #endif
 
 #if defined(__CUDA_ARCH__) && !defined(CSP_FE_PORTABLE)
@@ -30,11 +32,31 @@
 #define CSP_FE_PTX 0
 #endif
 
+// Carry-chain implementations (fe_chain.cuh): PTX on the device, emulated carry flag on the host when
+// CSP_FE_EMUL is defined (tests/hostcheck builds both the portable and the emulated variant).
+#if (defined(__CUDA_ARCH__) && !defined(CSP_FE_PORTABLE)) || defined(CSP_FE_EMUL)
+#define CSP_CHAIN 1
+#else
+#define CSP_CHAIN 0
+#endif
+
 namespace csp {
 
 struct fe {
   uint32_t v[8];
 };
+
+#if defined(__CUDACC__)
+namespace cc {
+__constant__ uint32_t kzero_dev;   // never written: 0.  Opaque to the compiler (see fe_chain.cuh, after()).
+}
+#endif
+
+}  // namespace csp
+#if CSP_CHAIN
+#include "fe_chain.cuh"
+#endif
+namespace csp {
 
 // 2^256 mod p = 2^32 + 977
 #define CSP_PC_LO 977u
@@ -68,6 +90,10 @@ CSP_HD uint32_t fe_add_kc(fe &r, uint32_t k) {
 
 // r = a + b (mod p), weakly reduced
 CSP_HD void fe_add(fe &r, const fe &a, const fe &b) {
+#if CSP_CHAIN
+  chain_add(r, a, b);
+  return;
+#endif
   uint64_t c = 0;
 #pragma unroll
   for (int i = 0; i < 8; i++) {
@@ -88,6 +114,10 @@ CSP_HD void fe_add(fe &r, const fe &a, const fe &b) {
 
 // r = a - b (mod p), weakly reduced
 CSP_HD void fe_sub(fe &r, const fe &a, const fe &b) {
+#if CSP_CHAIN
+  chain_sub(r, a, b);
+  return;
+#endif
   int64_t c = 0;
 #pragma unroll
   for (int i = 0; i < 8; i++) {
@@ -125,7 +155,13 @@ CSP_HD void fe_sub(fe &r, const fe &a, const fe &b) {
   }
 }
 
-CSP_HD void fe_dbl(fe &r, const fe &a) { fe_add(r, a, a); }
+CSP_HD void fe_dbl(fe &r, const fe &a) {
+#if CSP_CHAIN
+  chain_lin1<2>(r, a);
+#else
+  fe_add(r, a, a);
+#endif
+}
 
 // r = -a (mod p): 2p - a would overflow 2^256; use (p - a) when a <= p, else (2p - a) - 2^256 ... keep simple:
 CSP_HD void fe_neg(fe &r, const fe &a) {
@@ -294,6 +330,10 @@ CSP_HD void fe_mul_wide(uint32_t *t, const fe &a, const fe &b) {
 }
 
 CSP_HD void fe_mul(fe &r, const fe &a, const fe &b) {
+#if CSP_CHAIN
+  chain_mul(r, a, b);
+  return;
+#endif
   uint32_t t[16];
   fe_mul_wide(t, a, b);
   fe_fold512(r, t);
@@ -358,6 +398,10 @@ CSP_HD void fe_sqr_wide(uint32_t *t, const fe &a) {
 }
 
 CSP_HD void fe_sqr(fe &r, const fe &a) {
+#if CSP_CHAIN
+  chain_sqr(r, a);
+  return;
+#endif
   uint32_t t[16];
   fe_sqr_wide(t, a);
   fe_fold512(r, t);

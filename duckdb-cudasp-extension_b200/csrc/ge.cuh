@@ -54,6 +54,12 @@ CSP_HD void fe_fold_signed_top(fe &r, int64_t top) {
 }
 template <int KA, int KB>
 CSP_HD void fe_lin2(fe &r, const fe &a, const fe &b) {
+#if CSP_CHAIN
+  if (lin_ok_first(KA) && lin_ok(KB)) {
+    chain_lin2<(lin_ok_first(KA) ? KA : 1), (lin_ok(KB) ? KB : 1)>(r, a, b);
+    return;
+  }
+#endif
   int64_t c = 0;
 #pragma unroll
   for (int i = 0; i < 8; i++) {
@@ -65,6 +71,12 @@ CSP_HD void fe_lin2(fe &r, const fe &a, const fe &b) {
 }
 template <int KA, int KB, int KC>
 CSP_HD void fe_lin3(fe &r, const fe &a, const fe &b, const fe &c3) {
+#if CSP_CHAIN
+  if (lin_ok_first(KA) && lin_ok(KB) && lin_ok(KC)) {
+    chain_lin3<(lin_ok_first(KA) ? KA : 1), (lin_ok(KB) ? KB : 1), (lin_ok(KC) ? KC : 1)>(r, a, b, c3);
+    return;
+  }
+#endif
   int64_t c = 0;
 #pragma unroll
   for (int i = 0; i < 8; i++) {
@@ -76,6 +88,12 @@ CSP_HD void fe_lin3(fe &r, const fe &a, const fe &b, const fe &c3) {
 }
 template <int KA>
 CSP_HD void fe_lin1(fe &r, const fe &a) {
+#if CSP_CHAIN
+  if (lin_ok_first(KA)) {
+    chain_lin1<(lin_ok_first(KA) ? KA : 1)>(r, a);
+    return;
+  }
+#endif
   int64_t c = 0;
 #pragma unroll
   for (int i = 0; i < 8; i++) {

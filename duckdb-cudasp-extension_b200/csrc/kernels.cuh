@@ -27,20 +27,23 @@ struct SmemTab {
 };
 static const int LADDER_SMEM_WORDS_PER_THREAD = 4 * 3 * 8;
 
-template <int BLOCK, int MINB>
+template <int BLOCK, int MINB, int SYNC>
 __global__ void __launch_bounds__(BLOCK, MINB) k_ladder(const uint8_t *__restrict__ tweaks, fe *__restrict__ outX,
                                                         fe *__restrict__ outY, fe *__restrict__ outZ, uint32_t rows,
                                                         const __grid_constant__ LadderParams prm) {
   extern __shared__ uint32_t smem_tab[];
-  const uint32_t row = blockIdx.x * BLOCK + threadIdx.x;
-  if (row >= rows) return;
+  uint32_t row = blockIdx.x * BLOCK + threadIdx.x;
+  const bool live = row < rows;
+  if (!SYNC && !live) return;
+  if (!live) row = rows - 1;            // SYNC: every thread reaches every barrier; dead threads redo the last row
   SmemTab<BLOCK> tab;
   tab.base = smem_tab + threadIdx.x;
   ge P;
   load_fe_ro(P.x, reinterpret_cast<const fe *>(tweaks + (size_t)row * 64));
   load_fe_ro(P.y, reinterpret_cast<const fe *>(tweaks + (size_t)row * 64 + 32));
   gej acc;
-  ladder_row(acc, P, prm, tab);
+  ladder_row<SmemTab<BLOCK>, SYNC>(acc, P, prm, tab);
+  if (!live) return;
   store_fe(outX + row, acc.x);
   store_fe(outY + row, acc.y);
   store_fe(outZ + row, acc.z);

@@ -67,7 +67,9 @@ CSP_HD void store_fe(fe *p, const fe &r) {
 // Tab: storage for the 4-entry odd-multiples table, components 0 = x, 1 = beta*x, 2 = y;
 //      needs  uint32_t get(e, c, l)  and  void set(e, c, l, v).
 // Result: Jacobian S (not normalised to Z = 1; the caller batches the inversion).
-template <class Tab>
+// SYNC != 0 (device only): a block-wide barrier before every op keeps the block's warps on the same
+// instructions, so that they share instruction-cache lines (the unrolled loop body is larger than the I-cache).
+template <class Tab, int SYNC = 0>
 CSP_HD void ladder_row(gej &acc, const ge &P, const LadderParams &prm, Tab &tab) {
   // d = 2P (Jacobian).  Work on the curve isomorphic by dz, where d is affine.
   gej d;
@@ -124,6 +126,9 @@ CSP_HD void ladder_row(gej &acc, const ge &P, const LadderParams &prm, Tab &tab)
   fe_set_zero(acc.x); fe_set_zero(acc.y); fe_set_zero(acc.z);
   for (int i = 0; i < prm.nops; i++) {
     const uint32_t op = prm.ops[i];
+#if defined(__CUDA_ARCH__)
+    if (SYNC) __syncthreads();
+#endif
     if (op & 0x80u) {
       gej_dbl(acc, acc);
     } else {

@@ -9,24 +9,30 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = os.path.join(ROOT, "tests", "hostcheck", "host_check.cpp")
 SO = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck.so")
+SO_EMUL = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck_emul.so")   # -DCSP_FE_EMUL: the device carry-chain code, emulated
 CSRC = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "csrc")
 _lib = None
 
 
 def build(force=False):
-    deps = [SRC] + [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
-    if force or not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(d) for d in deps):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-I", CSRC,
-                               "-Wno-unknown-pragmas", "-o", SO, SRC])
+    deps = [SRC] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".hpp"))]
+    newest = max(os.path.getmtime(d) for d in deps)
+    for so, extra in ((SO, []), (SO_EMUL, ["-DCSP_FE_EMUL"])):
+        if force or not os.path.exists(so) or os.path.getmtime(so) < newest:
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-I", CSRC,
+                                   "-Wno-unknown-pragmas"] + extra + ["-o", so, SRC])
     return SO
 
 
+_libs = {}
+EMUL = False   # module-wide switch used by the parametrised tests: True -> the emulated carry-chain build
+
+
 def load():
-    global _lib
-    if _lib is None:
+    if EMUL not in _libs:
         build()
-        _lib = C.CDLL(SO)
-    return _lib
+        _libs[EMUL] = C.CDLL(SO_EMUL if EMUL else SO)
+    return _libs[EMUL]
 
 
 def _p(a, t=C.c_uint8):

@@ -47,6 +47,12 @@ int hc_field(int op, const uint8_t *a, const uint8_t *b, uint8_t *out, uint32_t 
       case 7: fe_lin2<1, -8>(r, x, y); break;
       case 8: fe_lin3<1, -1, -2>(r, x, y, y); break;
       case 9: fe_lin2<4, -1>(r, x, y); break;
+      case 10: fe_lin1<2>(r, x); break;
+      case 11: fe_lin1<3>(r, x); break;
+      case 12: fe_lin2<1, -2>(r, x, y); break;
+      case 13: fe_lin3<1, -1, -1>(r, x, y, y); break;
+      case 14: fe_dbl(r, x); break;
+      case 15: fe_lin2<3, 8>(r, x, y); break;
       default: r = x; break;
     }
     fe_to_le_bytes(out + 32 * (size_t)i, r);

@@ -18,6 +18,15 @@ def I(h):
     return int(h, 16)
 
 
+@pytest.fixture(autouse=True, params=["portable", "chain-emulated"])
+def fe_variant(request):
+    """Every test runs twice: against the portable 64-bit field code and against the device carry-chain code
+    (fe_chain.cuh) compiled for the host with an emulated carry flag."""
+    H.EMUL = request.param == "chain-emulated"
+    yield
+    H.EMUL = False
+
+
 def test_field_kats(golden):
     ks = golden["field"]
     a, b = [I(k["a"]) for k in ks], [I(k["b"]) for k in ks]
@@ -46,6 +55,12 @@ def test_field_weak_inputs_and_edges():
     assert H.field(7, a, b) == [(x - 8 * y) % P for x, y in zip(a, b)]
     assert H.field(8, a, b) == [(x - 3 * y) % P for x, y in zip(a, b)]
     assert H.field(9, a, b) == [(4 * x - y) % P for x, y in zip(a, b)]
+    assert H.field(10, a, b) == [2 * x % P for x in a]
+    assert H.field(11, a, b) == [3 * x % P for x in a]
+    assert H.field(12, a, b) == [(x - 2 * y) % P for x, y in zip(a, b)]
+    assert H.field(13, a, b) == [(x - 2 * y) % P for x, y in zip(a, b)]
+    assert H.field(14, a, b) == [2 * x % P for x in a]
+    assert H.field(15, a, b) == [(3 * x + 8 * y) % P for x, y in zip(a, b)]
     assert H.field(5, vals, vals) == [x % P for x in vals]
 
 
