@@ -1,5 +1,5 @@
 // host_ec.hpp -- host-side (CPU) curve helpers used ONLY for once-per-process / once-per-query
-// precomputation: the fixed-base table gtab[w][d] = (d*2^(8w) + r_w)*G, the spend-key adjustment
+// precomputation: the fixed-base table gtab[w][d] = (d*2^(13w) + r_w)*G, the spend-key adjustment
 // B_spend - (sum r_w)*G, and the SHA-256 tag midstate.  They run the same fe.cuh / ge.cuh code the
 // kernels run (portable path), with complete (checked) addition.  No row data ever goes through
 // these functions; they are not a CPU fallback for the scan.
@@ -149,16 +149,33 @@ inline void build_gtab(std::vector<ge> &table, Big &offset_sum, int wbits, int n
   const Big n = N_ORDER();
   HPoint base = generator();   // 2^(wbits*w) * G
   offset_sum = Big();
+  std::vector<gej> jac((size_t)entries);
+  std::vector<fe> pre((size_t)entries);
   for (int w = 0; w < nwin; w++) {
     Big rw = gtab_offset(w);
     offset_sum = mod(add(offset_sum, rw), n);
-    HPoint cur = h_mul(rw, generator());
-    // Jacobian running sum + one batch inversion per window would be faster; the table is built once
-    // per process and 8192 affine additions take a few milliseconds.
-    for (int d = 0; d < entries; d++) {
-      table[(size_t)w * entries + d].x = cur.x;
-      table[(size_t)w * entries + d].y = cur.y;
-      cur = h_add(cur, base);
+    HPoint first = h_mul(rw, generator());
+    // Jacobian running sum cur += base, then ONE inversion for the whole window (Montgomery's trick).
+    // The offsets make every partial sum a pseudo-random multiple of G: +-base or infinity cannot occur
+    // (checked below through Z != 0, which the incomplete addition would produce on a collision).
+    jac[0].x = first.x; jac[0].y = first.y; fe_set_u32(jac[0].z, 1);
+    for (int d = 1; d < entries; d++) gej_add_ge(jac[d], jac[d - 1], base.x, base.y);
+    fe acc;
+    fe_set_u32(acc, 1);
+    for (int d = 0; d < entries; d++) { pre[d] = acc; fe_mul(acc, acc, jac[d].z); }
+    fe inv;
+    fe_inv(inv, acc);
+    for (int d = entries - 1; d >= 0; d--) {
+      fe zi, zi2, zi3;
+      fe_mul(zi, inv, pre[d]);
+      fe_mul(inv, inv, jac[d].z);
+      fe_sqr(zi2, zi);
+      fe_mul(zi3, zi2, zi);
+      ge &e = table[(size_t)w * entries + d];
+      fe_mul(e.x, jac[d].x, zi2);
+      fe_mul(e.y, jac[d].y, zi3);
+      fe_normalize(e.x);
+      fe_normalize(e.y);
     }
     for (int b = 0; b < wbits; b++) base = h_dbl(base);
   }

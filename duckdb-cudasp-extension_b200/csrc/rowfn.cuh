@@ -15,9 +15,17 @@
 namespace csp {
 
 static const int LADDER_MAX_OPS_DEV = 240;
-static const int GTAB_WBITS = 8;                       // fixed-base window width
-static const int GTAB_NWIN = 256 / GTAB_WBITS;         // 32 windows
-static const int GTAB_ENTRIES = 1 << GTAB_WBITS;
+static const int GTAB_WBITS = 13;                                      // fixed-base window width
+static const int GTAB_NWIN = (256 + GTAB_WBITS - 1) / GTAB_WBITS;      // 20 windows -> 19 mixed additions per row
+static const int GTAB_ENTRIES = 1 << GTAB_WBITS;                       // 20 * 8192 * 64 B = 10 MB, L2-resident
+
+// digit w of the 256-bit scalar t (little-endian limbs): bits [w*WBITS, w*WBITS + WBITS)
+CSP_HD uint32_t gtab_digit(const fe &t, int w) {
+  const int bit = w * GTAB_WBITS, limb = bit >> 5, sh = bit & 31;
+  uint32_t v = t.v[limb] >> sh;
+  if (sh + GTAB_WBITS > 32 && limb < 7) v |= t.v[limb + 1] << (32 - sh);
+  return v & (uint32_t)(GTAB_ENTRIES - 1);
+}
 
 struct LadderParams {          // kernel parameter (constant bank): the per-query op list
   uint8_t ops[LADDER_MAX_OPS_DEV];
@@ -182,8 +190,8 @@ CSP_HD void batch_inv_thread(fe *vals, fe *scratch, uint32_t n, uint32_t T, uint
 // ---------------------------------------------------------------- K3 body: hash, t*G, + B_spend
 // in : shared secret S as Jacobian (X, Y) plus Zinv from the batch inversion
 // out: P0 = t*G + B_spend as Jacobian.
-// t*G uses the offset fixed-window table gtab[w][d] = (d * 2^(8w) + r_w) * G (affine, 64 B per
-// entry, 512 KB total, L2-resident): 31 mixed additions, no zero digits, no doublings.  The
+// t*G uses the offset fixed-window table gtab[w][d] = (d * 2^(13w) + r_w) * G (affine, 64 B per
+// entry, 20 x 8192 entries = 10 MB, L2-resident): 19 mixed additions, no zero digits, no doublings.  The
 // constant (sum r_w)*G is removed by adding spend_adj = B_spend - (sum r_w)*G instead of B_spend.
 // sx, sy, t_out (optional) receive the affine shared secret and the hash for the intermediates API.
 CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zinv, const ge *gtab, const FinalParams &fp,
@@ -205,15 +213,21 @@ CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zin
   fe t;
   bip352_shared_secret_hash(t, x, y.v[0] & 1u, fp.midstate);
   if (t_out) *t_out = t;
+  // all digits first (static limb indices: t stays in registers), then a one-entry-ahead prefetch pipeline
+  uint32_t dg[GTAB_NWIN];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int w = 0; w < GTAB_NWIN; w++) dg[w] = gtab_digit(t, w);
   {
-    const ge *q = gtab + (t.v[0] & 0xffu);
+    const ge *q = gtab + dg[0];
     load_fe_ro(acc.x, &q->x);
     load_fe_ro(acc.y, &q->y);
     fe_set_u32(acc.z, 1);
   }
   fe qx, qy;
   {
-    const ge *q = gtab + GTAB_ENTRIES + ((t.v[0] >> 8) & 0xffu);
+    const ge *q = gtab + GTAB_ENTRIES + dg[1];
     load_fe_ro(qx, &q->x);
     load_fe_ro(qy, &q->y);
   }
@@ -223,8 +237,7 @@ CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zin
   for (int w = 1; w < GTAB_NWIN; w++) {
     fe nx, ny;
     if (w + 1 < GTAB_NWIN) {   // prefetch the next window's entry while this addition runs
-      const uint32_t dgt = (t.v[(w + 1) >> 2] >> (((w + 1) & 3) * 8)) & 0xffu;
-      const ge *q = gtab + (size_t)(w + 1) * GTAB_ENTRIES + dgt;
+      const ge *q = gtab + (size_t)(w + 1) * GTAB_ENTRIES + dg[w + 1];
       load_fe_ro(nx, &q->x);
       load_fe_ro(ny, &q->y);
     } else {

@@ -111,6 +111,19 @@ def gtab_entry(w, d):
     return out.tobytes()
 
 
+def gtab_shape():
+    lib = load()
+    a, b = C.c_int(), C.c_int()
+    lib.hc_gtab_shape(C.byref(a), C.byref(b))
+    return a.value, b.value
+
+
+def gtab_digit(t, w):
+    lib = load()
+    lib.hc_gtab_digit.restype = C.c_uint32
+    return int(lib.hc_gtab_digit(_p(_b(t.to_bytes(32, "little"))), w))
+
+
 def gtab_offset(w):
     lib = load()
     out = np.zeros(32, np.uint8)

@@ -106,9 +106,21 @@ def test_ladder_g_multiples(golden):
 
 
 def test_gtab_entries():
-    for w, d in [(0, 0), (0, 1), (0, 255), (1, 0), (5, 77), (31, 255)]:
-        want = R.pt_mul((d << (8 * w)) + H.gtab_offset(w), R.G)
+    wbits, nwin = H.gtab_shape()
+    assert wbits * nwin >= 256
+    top = (1 << wbits) - 1
+    for w, d in [(0, 0), (0, 1), (0, top), (1, 0), (5, 77), (nwin - 1, 3), (nwin // 2, top), (nwin - 1, top)]:
+        want = R.pt_mul(((d << (wbits * w)) + H.gtab_offset(w)) % N, R.G)
         assert R.parse_point(H.gtab_entry(w, d)) == want
+
+
+def test_gtab_digits_cover_the_scalar():
+    wbits, nwin = H.gtab_shape()
+    rng = random.Random(11)
+    for t in [0, 1, (1 << 256) - 1, 1 << 255, (1 << 13) - 1, 1 << 13] + [rng.randrange(1 << 256) for _ in range(40)]:
+        digits = [H.gtab_digit(t, w) for w in range(nwin)]
+        assert all(0 <= d < (1 << wbits) for d in digits)
+        assert sum(d << (wbits * w) for w, d in enumerate(digits)) == t
 
 
 def test_pipeline_kats(golden):
