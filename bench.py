@@ -277,9 +277,10 @@ def main():
     launches = q.launch_count() - launches0
 
     # e2e: public host API, host buffers, copies inside the timed region
-    nb = len(batches)
-    h2d = rows * 64 + int(T["outputs"].shape[0]) * 8 + (rows + nb) * 4
-    d2h = sum((1 + min(b["cnt"], 1024)) * 4 for b in batches)
+    piece = min(args.batch, 131072)                 # SYNC_PIECE_ROWS in csrc/cudasp_capi.cu: the call streams in pieces
+    pieces = [min(piece, rows - b) for b in range(0, rows, piece)]
+    h2d = rows * 64 + int(T["outputs"].shape[0]) * 8 + (rows + len(pieces)) * 4
+    d2h = sum((1 + min(c, 1024)) * 4 for c in pieces)
     for _ in range(2):
         ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
     assert np.array_equal(ids, T["expected"]), "e2e match set differs from the planted matches"

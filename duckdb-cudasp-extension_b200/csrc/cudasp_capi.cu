@@ -29,6 +29,7 @@ thread_local std::string tl_err;
 
 const int SLOTS_PER_DEVICE = 3, MAX_SLOTS_PER_DEVICE = 64;
 const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
+const uint32_t SYNC_PIECE_ROWS = 131072;   // cudasp_scan_batch streams a large call in pieces of this many rows
 const int LADDER_BLOCK = 128, LADDER_MINB = 3;
 const int HASH_BLOCK = 128, HASH_MINB = 3;
 const int FINAL_BLOCK = 128;
@@ -40,6 +41,7 @@ struct Workspace {          // device-only scratch for one batch in flight
   uint8_t *flags = nullptr;
   cudaEvent_t free_evt = nullptr;                              // recorded after the last kernel using it
   uint32_t cap_rows = 0;
+  uint32_t cap_labels = 0;
 };
 
 struct Slot {
@@ -72,7 +74,9 @@ struct DevCtx {
   ge *d_gtab = nullptr;
   ge *d_labels = nullptr;
   cudaStream_t own_stream = nullptr;
-  std::vector<Slot *> slots;
+  std::vector<Slot *> slots;      // materialised so far (grown on demand up to max_slots)
+  uint32_t max_slots = 0;
+  uint32_t pending = 0;           // slots being allocated right now (outside the lock)
   uint32_t next_ws = 0;
 };
 
@@ -82,6 +86,7 @@ struct cudasp_query {
   host::QueryPlan plan;
   uint32_t n_labels = 0;
   uint32_t batch_rows = 0;
+  uint64_t max_outputs = 0;
   std::vector<DevCtx> devs;
   std::vector<Slot *> all_slots;
   std::mutex mu;
@@ -130,6 +135,7 @@ int get_device_gtab(cudasp_query *q, int device, ge **out) {
 
 int alloc_workspace(cudasp_query *q, Workspace &w, uint32_t rows, uint32_t L) {
   w.cap_rows = rows;
+  w.cap_labels = L;
   size_t n = (size_t)rows;
   CU(q, cudaMalloc(&w.X, n * sizeof(fe)));
   CU(q, cudaMalloc(&w.Y, n * sizeof(fe)));
@@ -188,6 +194,69 @@ uint32_t inv_threads(uint32_t n) {
   return std::max<uint32_t>(std::min<uint32_t>(t, n), 1u);
 }
 
+// ---- process-wide cache of staging slots -------------------------------------------------------
+// Pinned + device allocation of a slot costs tens of milliseconds; a host that runs many queries (DuckDB)
+// would pay it per query.  Destroyed queries park their slots here; new queries take them back when the
+// capacities fit.  cudasp_release_cached_memory() empties the cache.
+std::mutex g_cache_mu;
+std::vector<std::vector<Slot *>> g_cache;   // by device ordinal
+const size_t CACHE_MAX_PER_DEVICE = 40;
+
+Slot *cache_take(int device, uint32_t rows, uint64_t cap_outputs) {
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  if ((int)g_cache.size() <= device) return nullptr;
+  auto &v = g_cache[device];
+  for (size_t i = 0; i < v.size(); i++) {
+    Slot *s = v[i];
+    if (s->cap_rows >= rows && s->cap_rows <= std::max<uint64_t>(2ull * rows, 65536) && s->cap_outputs >= cap_outputs) {
+      v.erase(v.begin() + i);
+      return s;
+    }
+  }
+  return nullptr;
+}
+void cache_put(int device, Slot *s) {
+  {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    if ((int)g_cache.size() <= device) g_cache.resize(device + 1);
+    if (g_cache[device].size() < CACHE_MAX_PER_DEVICE) {
+      s->state = 0; s->internal = false; s->rows = 0; s->tag = 0;
+      g_cache[device].push_back(s);
+      return;
+    }
+  }
+  free_slot(*s);
+  delete s;
+}
+
+// A ready-to-use slot for this query on device index `di`: from the cache or freshly allocated.
+int materialise_slot(cudasp_query *q, int di, Slot **out) {
+  DevCtx &dc = q->devs[di];
+  const uint32_t L = q->n_labels;
+  CU(q, cudaSetDevice(dc.device));
+  Slot *s = cache_take(dc.device, q->batch_rows, q->max_outputs);
+  if (s) {
+    if (L > s->ws.cap_labels) {      // label scratch too small for this query: regrow it
+      cudaFree(s->ws.D); cudaFree(s->ws.DS); cudaFree(s->ws.flags);
+      s->ws.D = s->ws.DS = nullptr; s->ws.flags = nullptr;
+      const size_t n = (size_t)s->ws.cap_rows;
+      cudaError_t e = cudaMalloc(&s->ws.D, n * L * sizeof(fe));
+      if (e == cudaSuccess) e = cudaMalloc(&s->ws.DS, n * L * sizeof(fe));
+      if (e == cudaSuccess) e = cudaMalloc(&s->ws.flags, n);
+      if (e != cudaSuccess) { free_slot(*s); delete s; return fail(q, CUDASP_ERR_CUDA, cudaGetErrorString(e)); }
+      s->ws.cap_labels = L;
+    }
+  } else {
+    s = new Slot();
+    int rc = alloc_slot(q, *s, dc.device, q->batch_rows, q->max_outputs, L);
+    if (rc) { free_slot(*s); delete s; return rc; }
+  }
+  s->dev_index = di;
+  s->state = 0;
+  *out = s;
+  return 0;
+}
+
 // K1 launch shapes.  Variant 0 is the production default; the others exist for tuning and are selected
 // with the environment variable CUDASP_LADDER_VARIANT (read once per process).
 template <int BLOCK, int MINB, int SYNC>
@@ -212,10 +281,7 @@ void launch_ladder(int variant, const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, ui
     case 1: launch_ladder_t<128, 3, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
     case 2: launch_ladder_t<128, 4, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
     case 3: launch_ladder_t<128, 3, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
-    case 4: launch_ladder_t<384, 1, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
-    case 5: launch_ladder_t<512, 1, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
-    case 6: launch_ladder_t<256, 2, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
-    case 7: launch_ladder_t<512, 1, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 4: launch_ladder_t<256, 2, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
   }
 }
 
@@ -302,7 +368,7 @@ void cudasp_query_destroy(cudasp_query *q) {
   for (DevCtx &dc : q->devs) {
     cudaSetDevice(dc.device);
     cudaDeviceSynchronize();
-    for (Slot *s : dc.slots) { free_slot(*s); delete s; }
+    for (Slot *s : dc.slots) cache_put(dc.device, s);
     cudaFree(dc.d_labels);
     if (dc.own_stream) cudaStreamDestroy(dc.own_stream);
   }
@@ -344,9 +410,8 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
   if (rc) { delete q; return fail(nullptr, rc == -4 ? CUDASP_ERR_KEY : CUDASP_ERR_ARG, err); }
   q->n_labels = n_labels;
   q->batch_rows = batch_rows;
-  if (max_outputs_per_batch == 0) max_outputs_per_batch = 8ull * batch_rows;
+  if (max_outputs_per_batch == 0) max_outputs_per_batch = 4ull * batch_rows;
   q->devs.resize(devs.size());
-  uint32_t slot_id = 0;
   for (size_t i = 0; i < devs.size(); i++) {
     DevCtx &dc = q->devs[i];
     dc.device = devs[i];
@@ -359,18 +424,33 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
       if (e == cudaSuccess) e = cudaMemcpy(dc.d_labels, q->plan.labels.data(), n_labels * sizeof(ge), cudaMemcpyHostToDevice);
     }
     if (e != cudaSuccess) { cudasp_query_destroy(q); return fail(nullptr, CUDASP_ERR_CUDA, cudaGetErrorString(e)); }
-    for (uint32_t k = 0; k < slots_per_device; k++) {
-      Slot *s = new Slot();
-      s->id = slot_id++;
-      s->dev_index = (int)i;
-      dc.slots.push_back(s);
-      q->all_slots.push_back(s);
-      rc = alloc_slot(nullptr, *s, dc.device, batch_rows, max_outputs_per_batch, n_labels);
-      if (rc) { std::string m = tl_err; cudasp_query_destroy(q); return fail(nullptr, rc, m); }
-    }
+    dc.max_slots = slots_per_device;
+  }
+  q->max_outputs = max_outputs_per_batch;
+  q->all_slots.reserve(devs.size() * slots_per_device);   // never reallocates: ids stay valid without the lock
+  for (size_t i = 0; i < devs.size(); i++) {             // one slot per device now, the rest on demand
+    Slot *s = nullptr;
+    rc = materialise_slot(q, (int)i, &s);
+    if (rc) { std::string m = tl_err; cudasp_query_destroy(q); return fail(nullptr, rc, m); }
+    s->id = (uint32_t)q->all_slots.size();
+    q->devs[i].slots.push_back(s);
+    q->all_slots.push_back(s);
   }
   *out = q;
   return CUDASP_OK;
+}
+
+void cudasp_release_cached_memory(void) {
+  std::vector<std::vector<Slot *>> old;
+  {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    old.swap(g_cache);
+  }
+  for (size_t d = 0; d < old.size(); d++) {
+    if (old[d].empty()) continue;
+    cudaSetDevice((int)d);
+    for (Slot *s : old[d]) { free_slot(*s); delete s; }
+  }
 }
 
 uint64_t cudasp_launch_count(const cudasp_query *q) { return q ? q->launches.load() : 0; }
@@ -391,26 +471,77 @@ int cudasp_query_info(const cudasp_query *q, int *n_devices, int *ladder_dbl, in
 namespace {
 
 // ---- slot pool ------------------------------------------------------------------------
-Slot *try_acquire_locked(cudasp_query *q) {
-  const size_t n = q->all_slots.size();
-  // interleave devices: slot ids are device-major, so walk with a stride of SLOTS_PER_DEVICE
-  for (size_t k = 0; k < n; k++) {
-    size_t idx = (q->rr + k) % n;
-    size_t dev = idx % q->devs.size(), j = idx / q->devs.size();
-    Slot *s = q->devs[dev].slots[j];
-    if (s->state == 0) {
-      s->state = 1;
-      q->rr = (uint32_t)((idx + 1) % n);
-      return s;
+// A free slot, devices taken in turn; when every materialised slot is busy and a device is below its
+// limit, a new slot is materialised (cache or allocation) OUTSIDE the lock.  nullptr = all busy, at the limit.
+Slot *try_acquire(cudasp_query *q, int *err) {
+  *err = 0;
+  int grow_dev = -1;
+  {
+    std::lock_guard<std::mutex> lk(q->mu);
+    const size_t nd = q->devs.size();
+    for (size_t k = 0; k < nd; k++) {
+      DevCtx &dc = q->devs[(q->rr + k) % nd];
+      for (Slot *s : dc.slots) {
+        if (s->state == 0) {
+          s->state = 1;
+          q->rr = (uint32_t)((q->rr + k + 1) % nd);
+          return s;
+        }
+      }
     }
+    size_t best = SIZE_MAX;
+    for (size_t k = 0; k < nd; k++) {
+      DevCtx &dc = q->devs[(q->rr + k) % nd];
+      const size_t have = dc.slots.size() + dc.pending;
+      if (have < dc.max_slots && have < best) { best = have; grow_dev = (int)((q->rr + k) % nd); }
+    }
+    if (grow_dev < 0) return nullptr;
+    q->devs[grow_dev].pending++;
   }
-  return nullptr;
-}
-Slot *acquire_blocking(cudasp_query *q) {
-  std::unique_lock<std::mutex> lk(q->mu);
-  Slot *s;
-  while (!(s = try_acquire_locked(q))) q->cv.wait(lk);
+  Slot *s = nullptr;
+  int rc = materialise_slot(q, grow_dev, &s);
+  std::lock_guard<std::mutex> lk(q->mu);
+  q->devs[grow_dev].pending--;
+  if (rc) { *err = rc; return nullptr; }
+  s->id = (uint32_t)q->all_slots.size();
+  s->state = 1;
+  q->devs[grow_dev].slots.push_back(s);
+  q->all_slots.push_back(s);
+  q->rr = (uint32_t)((grow_dev + 1) % q->devs.size());
   return s;
+}
+Slot *acquire_blocking(cudasp_query *q, int *err) {
+  for (;;) {
+    Slot *s = try_acquire(q, err);
+    if (s || *err) return s;
+    std::unique_lock<std::mutex> lk(q->mu);
+    bool any_free = false;
+    for (Slot *t : q->all_slots) any_free |= (t->state == 0);
+    if (!any_free) q->cv.wait(lk);
+  }
+}
+// at least min(n, max_slots) slots materialised on device index di (their workspaces are what scan_device borrows)
+int ensure_slots(cudasp_query *q, int di, uint32_t n) {
+  for (;;) {
+    {
+      std::lock_guard<std::mutex> lk(q->mu);
+      DevCtx &dc = q->devs[di];
+      if (dc.slots.size() + dc.pending >= std::min<uint32_t>(n, dc.max_slots)) return 0;
+      dc.pending++;
+    }
+    Slot *s = nullptr;
+    int rc = materialise_slot(q, di, &s);
+    std::lock_guard<std::mutex> lk(q->mu);
+    q->devs[di].pending--;
+    if (rc) return rc;
+    s->id = (uint32_t)q->all_slots.size();
+    q->devs[di].slots.push_back(s);
+    q->all_slots.push_back(s);
+  }
+}
+Slot *slot_by_id(cudasp_query *q, uint32_t id) {
+  std::lock_guard<std::mutex> lk(q->mu);
+  return id < q->all_slots.size() ? q->all_slots[id] : nullptr;
 }
 void release_slot(cudasp_query *q, Slot *s) {
   {
@@ -468,7 +599,9 @@ extern "C" {
 // ---- streaming API --------------------------------------------------------------------
 int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
   if (!q || !slot) return fail(q, CUDASP_ERR_ARG, "NULL argument");
-  Slot *s = acquire_blocking(q);
+  int err = 0;
+  Slot *s = acquire_blocking(q, &err);
+  if (!s) return err;
   slot->slot_id = s->id;
   slot->device = q->devs[s->dev_index].device;
   slot->tweak_keys = s->h_tweaks;
@@ -481,11 +614,9 @@ int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
 
 int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
   if (!q || !slot) return fail(q, CUDASP_ERR_ARG, "NULL argument");
-  Slot *s;
-  {
-    std::lock_guard<std::mutex> lk(q->mu);
-    s = try_acquire_locked(q);
-  }
+  int err = 0;
+  Slot *s = try_acquire(q, &err);
+  if (err) return err;
   if (!s) return 0;
   slot->slot_id = s->id;
   slot->device = q->devs[s->dev_index].device;
@@ -498,8 +629,9 @@ int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
 }
 
 int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag) {
-  if (!q || !slot || slot->slot_id >= q->all_slots.size()) return fail(q, CUDASP_ERR_ARG, "bad slot");
-  Slot *s = q->all_slots[slot->slot_id];
+  if (!q || !slot) return fail(q, CUDASP_ERR_ARG, "bad slot");
+  Slot *s = slot_by_id(q, slot->slot_id);
+  if (!s) return fail(q, CUDASP_ERR_ARG, "bad slot");
   if (s->state != 1) return fail(q, CUDASP_ERR_STATE, "slot was not acquired");
   if (rows > s->cap_rows || n_outputs > s->cap_outputs) return fail(q, CUDASP_ERR_ARG, "rows/outputs exceed the slot capacity");
   if (rows && s->h_off[rows] != n_outputs) return fail(q, CUDASP_ERR_ARG, "out_offsets[rows] != n_outputs");
@@ -541,8 +673,9 @@ int cudasp_poll(cudasp_query *q, cudasp_result *r) { return take_result(q, r, fa
 int cudasp_wait(cudasp_query *q, cudasp_result *r) { return take_result(q, r, true); }
 
 int cudasp_release_result(cudasp_query *q, const cudasp_result *r) {
-  if (!q || !r || r->slot_id >= q->all_slots.size()) return fail(q, CUDASP_ERR_ARG, "bad result");
-  Slot *s = q->all_slots[r->slot_id];
+  if (!q || !r) return fail(q, CUDASP_ERR_ARG, "bad result");
+  Slot *s = slot_by_id(q, r->slot_id);
+  if (!s) return fail(q, CUDASP_ERR_ARG, "bad result");
   if (s->state != 3) return fail(q, CUDASP_ERR_STATE, "result was not handed out");
   release_slot(q, s);
   return CUDASP_OK;
@@ -570,22 +703,23 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
     release_slot(q, p.s);
     return r;
   };
-  for (uint32_t base = 0; base < rows && !rc; base += q->batch_rows) {
-    const uint32_t cnt = std::min<uint32_t>(q->batch_rows, rows - base);
+  // Pieces smaller than batch_rows: the first H2D copy is short, so the GPU starts early, and the memcpy of
+  // piece k+1 into pinned memory overlaps the kernels of piece k (separate slots, separate streams).
+  const uint32_t piece = std::min<uint32_t>(q->batch_rows, SYNC_PIECE_ROWS);
+  for (uint32_t base = 0; base < rows && !rc; base += piece) {
+    const uint32_t cnt = std::min<uint32_t>(piece, rows - base);
     Slot *s = nullptr;
     while (!s) {
-      {
-        std::lock_guard<std::mutex> lk(q->mu);
-        s = try_acquire_locked(q);
-      }
-      if (s) break;
+      s = try_acquire(q, &rc);
+      if (s || rc) break;
       if (!pending.empty()) {          // recycle our own oldest batch (results stay in row order)
         Pending p = pending.front();
         pending.pop_front();
         rc = collect(p);
         if (rc) break;
       } else {
-        s = acquire_blocking(q);
+        s = acquire_blocking(q, &rc);
+        if (!s) break;
       }
     }
     if (rc) break;
@@ -633,6 +767,8 @@ int cudasp_scan_device(cudasp_query *q, int device, const uint8_t *d_tweak_keys,
   cudaStream_t st = stream ? (cudaStream_t)stream : dc->own_stream;
   // borrow the scratch of one of the device's slots, round robin; ordering between users of the
   // same scratch is enforced with its free_evt, so any stream may be used.
+  int rc0 = ensure_slots(q, (int)(dc - q->devs.data()), 3);
+  if (rc0) return rc0;
   Workspace *w;
   {
     std::lock_guard<std::mutex> lk(q->mu);
@@ -680,9 +816,10 @@ static int scan_debug(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows,
   const uint32_t L = q->n_labels;
   for (uint32_t base = 0; base < rows; base += q->batch_rows) {
     const uint32_t cnt = std::min<uint32_t>(q->batch_rows, rows - base);
-    Slot *s = acquire_blocking(q);
-    DevCtx &dc = q->devs[s->dev_index];
     int rc = 0;
+    Slot *s = acquire_blocking(q, &rc);
+    if (!s) return rc;
+    DevCtx &dc = q->devs[s->dev_index];
     int64_t *d_c = nullptr;
     uint8_t *d_S = nullptr, *d_t = nullptr, *d_P = nullptr;
     auto body = [&]() -> int {

@@ -17,6 +17,9 @@
 #include "duckdb/parallel/task_scheduler.hpp"
 
 #include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -79,11 +82,22 @@ struct CudaspScanLocalState : public LocalTableFunctionState {
 	bool finalized = false;
 	bool is_output_thread = false;
 	bool have_slot = false;
+	double accumulate_s = 0, first_input = 0;
+	uint64_t rows_seen = 0, batches = 0;
 	cudasp_slot slot;
 	uint32_t rows = 0;
 	uint64_t n_outputs = 0;
 	unique_ptr<InFlightBatch> meta;
 };
+
+// CUDASP_TRACE=1 prints coarse host-side timings to stderr (query setup, per-worker accumulate time, final drain)
+bool TraceOn() {
+	static const bool on = getenv("CUDASP_TRACE") != nullptr;
+	return on;
+}
+double NowSec() {
+	return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 [[noreturn]] void ThrowGpu(CudaspScanState &state, const char *what) {
 	const char *msg = cudasp_last_error(state.query);
@@ -182,6 +196,7 @@ static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &contex
 	while (slots > 3 && (uint64_t)slots * bind.batch_size > 48000000ull) {
 		slots--;
 	}
+	const double t_create = NowSec();
 	int rc = cudasp_query_create_ex(const_data_ptr_cast(bind.scan_private_key.data()),
 	                                const_data_ptr_cast(bind.spend_public_key.data()),
 	                                bind.n_labels ? const_data_ptr_cast(bind.label_keys.data()) : nullptr, bind.n_labels,
@@ -192,6 +207,10 @@ static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &contex
 			throw InvalidInputException("cudasp_scan: %s", msg ? msg : "invalid keys");
 		}
 		throw IOException("cudasp_scan: GPU initialisation failed: %s", msg ? msg : "unknown error");
+	}
+	if (TraceOn()) {
+		fprintf(stderr, "[cudasp] query_create: %.3f s (%u slots/device, %d devices, %llu threads)\n", NowSec() - t_create, slots,
+		        n_dev, (unsigned long long)threads);
 	}
 	return std::move(state);
 }
@@ -387,8 +406,16 @@ static OperatorResultType CudaspScanFunction(ExecutionContext &context, TableFun
 	auto &state = data_p.global_state->Cast<CudaspScanState>();
 	auto &local = data_p.local_state->Cast<CudaspScanLocalState>();
 	if (input.size() > 0) {
+		const double t0 = TraceOn() ? NowSec() : 0;
+		if (TraceOn() && local.rows_seen == 0) {
+			local.first_input = t0;
+		}
 		AccumulateInput(state, local, bind, input);
 		Drain(state, false);
+		if (TraceOn()) {
+			local.accumulate_s += NowSec() - t0;
+			local.rows_seen += input.size();
+		}
 	}
 	return OperatorResultType::NEED_MORE_INPUT;
 }
@@ -403,6 +430,10 @@ static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &cont
 	auto &local = data_p.local_state->Cast<CudaspScanLocalState>();
 
 	if (!local.finalized) {
+		if (TraceOn()) {
+			fprintf(stderr, "[cudasp] worker: %llu rows, accumulate+drain %.3f s, span %.3f s\n",
+			        (unsigned long long)local.rows_seen, local.accumulate_s, local.rows_seen ? NowSec() - local.first_input : 0.0);
+		}
 		SubmitSlot(state, local);
 		Drain(state, false);
 		std::lock_guard<std::mutex> guard(state.finalize_lock);
@@ -418,7 +449,11 @@ static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &cont
 			return OperatorFinalizeResultType::FINISHED;
 		}
 		local.is_output_thread = true;
+		const double t0 = NowSec();
 		Drain(state, true);  // barrier: every submitted batch has been collected after this
+		if (TraceOn()) {
+			fprintf(stderr, "[cudasp] final drain: %.3f s, %llu matches\n", NowSec() - t0, (unsigned long long)state.output_txids.size());
+		}
 	}
 
 	const idx_t remaining = state.output_txids.size() - state.output_position;

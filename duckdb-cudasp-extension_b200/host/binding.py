@@ -33,7 +33,7 @@ class Result(C.Structure):
 EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "cudasp_query_destroy", "cudasp_scan_batch",
            "cudasp_acquire_slot", "cudasp_submit_slot", "cudasp_poll", "cudasp_wait", "cudasp_release_result",
            "cudasp_scan_device", "cudasp_profile_stages", "cudasp_scan_candidates", "cudasp_scan_intermediates", "cudasp_test_field",
-           "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot"]
+           "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory"]
 
 
 def lib():

@@ -53,7 +53,10 @@ const char *cudasp_last_error(const cudasp_query *q);
  * (gECC gsv.h:1094-1122): recodes the fixed scan key (GLV + wNAF), uploads the fixed-base table,
  * allocates every device/pinned buffer for `batch_rows`-row batches on each listed device.
  *   devices == NULL  -> use devices 0..n_devices-1;  n_devices == 0 -> all visible devices.
- *   max_outputs_per_batch == 0 -> 8 * batch_rows (grown on demand by the synchronous call). */
+ *   max_outputs_per_batch == 0 -> 4 * batch_rows (grown on demand by the synchronous call; a streaming
+ *   producer cuts a batch early when the next row's outputs would not fit).
+ * Staging slots are materialised on demand (one per device at creation) and are parked in a process-wide
+ * cache by cudasp_query_destroy, so later queries do not pay the pinned/device allocations again. */
 int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64],
                         const uint8_t *label_keys /* n_labels * 64 B */, uint32_t n_labels,
                         const int *devices, int n_devices, uint32_t batch_rows,
@@ -66,6 +69,9 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
                            const uint8_t *label_keys, uint32_t n_labels, const int *devices, int n_devices,
                            uint32_t batch_rows, uint64_t max_outputs_per_batch, uint32_t slots_per_device,
                            cudasp_query **out);
+
+/* Frees the staging slots parked by destroyed queries (see above). */
+void cudasp_release_cached_memory(void);
 
 /* Replaces FreeBatchScanState (src/cudasp_gpu.cu:969-1023).  Waits for in-flight batches. */
 void cudasp_query_destroy(cudasp_query *q);

@@ -1,0 +1,83 @@
+#!/usr/bin/env python3
+"""End-to-end timing through the real DuckDB engine + the C++ `cudasp` extension (duckdb_ext/bin/duckdb):
+writes a synthetic Parquet table (planted matches), then times
+    SELECT count(*) FROM cudasp_scan((SELECT txid,height,tweak_key,outputs FROM read_parquet(...)), sk, spend, [labels])
+and, for comparison, the same scan of the table without the function (the cost of reading + decoding alone).
+
+    python tools/duckdb_e2e.py [--rows N] [--labels L] [--threads T] [--in-memory]       (GPU box)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+DUCKDB = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "duckdb_ext", "bin", "duckdb")
+
+
+def blob(b: bytes) -> str:
+    return "'" + "".join("\\x%02x" % c for c in b) + "'::BLOB"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=4000000)
+    ap.add_argument("--labels", type=int, default=1)
+    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--batch", type=int, default=300000)
+    ap.add_argument("--in-memory", action="store_true", help="load the table into a DuckDB table first (no Parquet decode in the timed query)")
+    a = ap.parse_args()
+    import numpy as np
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    from tests import synth
+    t0 = time.perf_counter()
+    T = synth.make_table(a.rows, 352003, n_labels=a.labels, n_base=100, n_per_label=100 if a.labels else 0, batch_rows=a.batch)
+    rows = a.rows
+    off = T["offsets"].astype(np.int64)
+    tw = pa.FixedSizeBinaryArray.from_buffers(pa.binary(64), rows, [None, pa.py_buffer(T["tweaks"].tobytes())]).cast(pa.binary())
+    txid = np.zeros((rows, 32), np.uint8)
+    txid[:, :8] = np.arange(rows, dtype=np.uint64).view(np.uint8).reshape(rows, 8)
+    tx = pa.FixedSizeBinaryArray.from_buffers(pa.binary(32), rows, [None, pa.py_buffer(txid.tobytes())]).cast(pa.binary())
+    outs = pa.ListArray.from_arrays(pa.array(off.astype(np.int32), pa.int32()), pa.array(T["outputs"], pa.int64()))
+    tbl = pa.table({"txid": tx, "height": pa.array((800000 + np.arange(rows) // 3000).astype(np.int32)), "tweak_key": tw, "outputs": outs})
+    d = tempfile.mkdtemp(prefix="cudasp_e2e_")
+    path = os.path.join(d, "t.parquet")
+    pq.write_table(tbl, path, row_group_size=122880, compression="NONE")
+    gen_s = time.perf_counter() - t0
+    labels = "[" + ", ".join(blob(l) for l in T["labels"]) + "]" + ("" if T["labels"] else "::BLOB[]")
+    src = "read_parquet('%s')" % path
+    pre = "PRAGMA threads=%d;\n" % a.threads if a.threads else ""
+    if a.in_memory:
+        pre += "CREATE TABLE t AS SELECT * FROM %s;\n" % src
+        src = "t"
+    scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM %s), %s, %s, %s, batch_size := %d);" % (
+        src, blob(T["sk"]), blob(T["spend"]), labels, a.batch)
+    plain = "SELECT count(*), sum(height), sum(octet_length(tweak_key)), sum(len(outputs)) FROM %s;" % src
+    sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + "SELECT current_setting('threads');\n"
+    p = subprocess.run([DUCKDB, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
+    if os.environ.get("CUDASP_TRACE"):
+        sys.stderr.write(p.stderr)
+    lines = [l for l in p.stdout.strip().splitlines() if l]
+    times = [float(l.split("real")[1].split()[0]) for l in lines if l.startswith("Run Time")]
+    vals = [l for l in lines if not l.startswith("Run Time")]
+    want = len(T["expected"])
+    ok = p.returncode == 0 and len(vals) >= 2 and int(vals[0]) == want and int(vals[1]) == want
+    res = {"rows": rows, "labels": a.labels, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
+           "matches_ok": ok, "scan_s_cold": times[0] if times else None, "scan_s_warm": times[1] if len(times) > 1 else None,
+           "plain_read_s": times[2] if len(times) > 2 else None, "gen_s": round(gen_s, 1),
+           "rows_per_s_warm": rows / times[1] if len(times) > 1 else None, "stderr": p.stderr[-300:]}
+    print(json.dumps(res))
+    try:
+        os.remove(path)
+        os.rmdir(d)
+    except OSError:
+        pass
+
+
+if __name__ == "__main__":
+    main()

@@ -45,7 +45,7 @@ if __name__ == "__main__":
     if os.environ.get("_LV_CHILD"):
         child()
     else:
-        variants = sys.argv[1:] or ["0", "1", "2", "3", "4", "5", "6", "7"]
+        variants = sys.argv[1:] or ["0", "1", "2", "3", "4"]
         for v in variants:
             env = dict(os.environ, CUDASP_LADDER_VARIANT=v, _LV_CHILD="1")
             p = subprocess.run([sys.executable, os.path.abspath(__file__)], env=env, capture_output=True, text=True, timeout=300)
