@@ -277,7 +277,8 @@ def main():
     launches = q.launch_count() - launches0
 
     # e2e: public host API, host buffers, copies inside the timed region
-    piece = min(args.batch, 131072)                 # SYNC_PIECE_ROWS in csrc/cudasp_capi.cu: the call streams in pieces
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    piece = min(args.batch, sms * 4 * 128 * 2)      # piece_rows in csrc/cudasp_capi.cu: the call streams in pieces of 2 K1 waves
     pieces = [min(piece, rows - b) for b in range(0, rows, piece)]
     h2d = rows * 64 + int(T["outputs"].shape[0]) * 8 + (rows + len(pieces)) * 4
     d2h = sum((1 + min(c, 1024)) * 4 for c in pieces)

@@ -29,7 +29,7 @@ thread_local std::string tl_err;
 
 const int SLOTS_PER_DEVICE = 3, MAX_SLOTS_PER_DEVICE = 64;
 const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
-const uint32_t SYNC_PIECE_ROWS = 131072;   // cudasp_scan_batch streams a large call in pieces of this many rows
+const uint32_t SYNC_PIECE_WAVES = 2;       // cudasp_scan_batch streams a large call in pieces of this many K1 waves
 const int LADDER_BLOCK = 128, LADDER_MINB = 3;
 const int HASH_BLOCK = 128, HASH_MINB = 3;
 const int FINAL_BLOCK = 128;
@@ -87,6 +87,7 @@ struct cudasp_query {
   uint32_t n_labels = 0;
   uint32_t batch_rows = 0;
   uint64_t max_outputs = 0;
+  uint32_t piece_rows = 0;       // rows per piece of the synchronous call: whole K1 waves (SMs x 4 blocks x 128 rows)
   std::vector<DevCtx> devs;
   std::vector<Slot *> all_slots;
   std::mutex mu;
@@ -427,6 +428,11 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
     dc.max_slots = slots_per_device;
   }
   q->max_outputs = max_outputs_per_batch;
+  {
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, devs[0]);
+    q->piece_rows = (uint32_t)sms * 4u * 128u * SYNC_PIECE_WAVES;
+  }
   q->all_slots.reserve(devs.size() * slots_per_device);   // never reallocates: ids stay valid without the lock
   for (size_t i = 0; i < devs.size(); i++) {             // one slot per device now, the rest on demand
     Slot *s = nullptr;
@@ -705,7 +711,7 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
   };
   // Pieces smaller than batch_rows: the first H2D copy is short, so the GPU starts early, and the memcpy of
   // piece k+1 into pinned memory overlaps the kernels of piece k (separate slots, separate streams).
-  const uint32_t piece = std::min<uint32_t>(q->batch_rows, SYNC_PIECE_ROWS);
+  const uint32_t piece = std::min<uint32_t>(q->batch_rows, q->piece_rows);
   for (uint32_t base = 0; base < rows && !rc; base += piece) {
     const uint32_t cnt = std::min<uint32_t>(piece, rows - base);
     Slot *s = nullptr;

@@ -40,10 +40,14 @@ def make_table(rows: int, seed: int, n_labels: int = 0, n_base: int = 100, n_per
     offsets[1:] = np.cumsum(n_out)
     outputs = nrng.integers(-(1 << 63), (1 << 63) - 1, int(offsets[-1]), dtype=np.int64)
     # planted rows: first/last row of every batch range + random ones
-    cand_rows = [r for r in range(rows) if r not in empty]
     edges = [r for b in range(0, rows, batch_rows) for r in (b, min(b + batch_rows, rows) - 1) if r not in empty]
     want = n_base + n_per_label * n_labels
-    pool = list(dict.fromkeys(edges + rng.sample(cand_rows, min(len(cand_rows), want + 40))))
+    if rows <= 100000:      # historical draw (keeps the small tables of the test-suite unchanged)
+        cand_rows = [r for r in range(rows) if r not in empty]
+        drawn = rng.sample(cand_rows, min(len(cand_rows), want + 40))
+    else:                   # large tables: sample from the range, then drop the few empty-output rows
+        drawn = [r for r in rng.sample(range(rows), min(rows, want + 60)) if r not in empty]
+    pool = list(dict.fromkeys(edges + drawn))
     planted = pool[:want]
     near = pool[want:want + 20] if specials else []
     sel = np.array(planted + near, dtype=np.int64)
