@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <atomic>
 #include <condition_variable>
@@ -27,7 +29,7 @@ namespace {
 
 thread_local std::string tl_err;
 
-const int SLOTS_PER_DEVICE = 3, MAX_SLOTS_PER_DEVICE = 64;
+const int SLOTS_PER_DEVICE = 6, MAX_SLOTS_PER_DEVICE = 64;   // 6: measured, a 3-deep queue lets the GPU run dry (profiles/r01e)
 const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
 const uint32_t SYNC_PIECE_WAVES = 2;       // cudasp_scan_batch streams a large call in pieces of this many K1 waves
 const int LADDER_BLOCK = 128, LADDER_MINB = 3;
@@ -49,6 +51,7 @@ struct Slot {
   int dev_index = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;
+  cudaEvent_t tr[3] = {nullptr, nullptr, nullptr};   // CUDASP_TRACE: before H2D, after H2D, after the last kernel
   // pinned host staging
   uint8_t *h_tweaks = nullptr;
   int64_t *h_outputs = nullptr;
@@ -171,6 +174,7 @@ int alloc_slot(cudasp_query *q, Slot &s, int device, uint32_t rows, uint64_t cap
   s.cap_rows = rows;
   CU(q, cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
   CU(q, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  for (int i = 0; i < 3; i++) CU(q, cudaEventCreate(&s.tr[i]));
   CU(q, cudaHostAlloc((void **)&s.h_tweaks, (size_t)rows * 64, cudaHostAllocDefault));
   CU(q, cudaHostAlloc((void **)&s.h_off, ((size_t)rows + 1) * 4, cudaHostAllocDefault));
   CU(q, cudaHostAlloc((void **)&s.h_result, ((size_t)rows + 1) * 4, cudaHostAllocDefault));
@@ -186,6 +190,7 @@ void free_slot(Slot &s) {
   cudaFree(s.d_tweaks); cudaFree(s.d_outputs); cudaFree(s.d_off); cudaFree(s.d_result);
   free_workspace(s.ws);
   if (s.done) cudaEventDestroy(s.done);
+  for (int i = 0; i < 3; i++) if (s.tr[i]) cudaEventDestroy(s.tr[i]);
   if (s.stream) cudaStreamDestroy(s.stream);
 }
 
@@ -386,7 +391,10 @@ int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_
 int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64], const uint8_t *label_keys,
                            uint32_t n_labels, const int *devices, int n_devices, uint32_t batch_rows,
                            uint64_t max_outputs_per_batch, uint32_t slots_per_device, cudasp_query **out) {
-  if (slots_per_device == 0) slots_per_device = SLOTS_PER_DEVICE;
+  if (slots_per_device == 0) {
+    const char *e = getenv("CUDASP_SLOTS");                   // tuning aid
+    slots_per_device = e && atoi(e) > 0 ? (uint32_t)atoi(e) : SLOTS_PER_DEVICE;
+  }
   if (slots_per_device > (uint32_t)MAX_SLOTS_PER_DEVICE) return fail(nullptr, CUDASP_ERR_ARG, "slots_per_device out of range");
   if (!out) return fail(nullptr, CUDASP_ERR_ARG, "out is NULL");
   *out = nullptr;
@@ -431,7 +439,9 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
   {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, devs[0]);
-    q->piece_rows = (uint32_t)sms * 4u * 128u * SYNC_PIECE_WAVES;
+    const char *pw = getenv("CUDASP_PIECE_WAVES");            // tuning aid
+    const uint32_t waves = pw && atoi(pw) > 0 ? (uint32_t)atoi(pw) : SYNC_PIECE_WAVES;
+    q->piece_rows = (uint32_t)sms * 4u * 128u * waves;
   }
   q->all_slots.reserve(devs.size() * slots_per_device);   // never reallocates: ids stay valid without the lock
   for (size_t i = 0; i < devs.size(); i++) {             // one slot per device now, the rest on demand
@@ -564,15 +574,19 @@ int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t
   cudaStream_t st = s->stream;
   s->rows = rows;
   s->tag = tag;
+  static const bool trace = getenv("CUDASP_TRACE") != nullptr;
+  if (trace) cudaEventRecord(s->tr[0], st);
   if (rows) {
     CU(q, cudaMemcpyAsync(s->d_tweaks, s->h_tweaks, (size_t)rows * 64, cudaMemcpyHostToDevice, st));
     CU(q, cudaMemcpyAsync(s->d_off, s->h_off, ((size_t)rows + 1) * 4, cudaMemcpyHostToDevice, st));
     if (n_outputs) CU(q, cudaMemcpyAsync(s->d_outputs, s->h_outputs, n_outputs * 8, cudaMemcpyHostToDevice, st));
   }
+  if (trace) cudaEventRecord(s->tr[1], st);
   CU(q, cudaStreamWaitEvent(st, s->ws.free_evt, 0));
   int rc = launch_pipeline(q, dc, s->ws, s->d_tweaks, s->d_outputs, s->d_off, rows, s->d_result + 1, s->d_result, st,
                            nullptr, nullptr, nullptr, nullptr);
   if (rc) return rc;
+  if (trace) cudaEventRecord(s->tr[2], st);
   CU(q, cudaEventRecord(s->ws.free_evt, st));
   const uint32_t eager = std::min<uint32_t>(rows, EAGER_IDS);
   CU(q, cudaMemcpyAsync(s->h_result, s->d_result, ((size_t)eager + 1) * 4, cudaMemcpyDeviceToHost, st));
@@ -585,6 +599,13 @@ int finish(cudasp_query *q, Slot *s, uint32_t *n_matches) {
   DevCtx &dc = q->devs[s->dev_index];
   CU(q, cudaSetDevice(dc.device));
   CU(q, cudaEventSynchronize(s->done));
+  static const bool trace = getenv("CUDASP_TRACE") != nullptr && getenv("CUDASP_TRACE")[0] == '2';
+  if (trace) {
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, s->tr[0], s->tr[1]);
+    cudaEventElapsedTime(&b, s->tr[1], s->tr[2]);
+    fprintf(stderr, "[cudasp] slot %u: %u rows, H2D %.3f ms, kernels %.3f ms\n", s->id, s->rows, a, b);
+  }
   uint32_t n = s->h_result[0];
   if (n > s->rows) return fail(q, CUDASP_ERR_STATE, "internal: match count exceeds rows");
   if (n > EAGER_IDS) {
@@ -699,9 +720,15 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
   std::deque<Pending> pending;
   uint32_t total = 0;
   int rc = 0;
+  static const bool trace = getenv("CUDASP_TRACE") != nullptr;     // coarse host-side timings to stderr
+  auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t_begin = trace ? now() : 0;
+  double t_copy = 0, t_submit = 0, t_wait = 0;
   auto collect = [&](Pending p) -> int {
     uint32_t n = 0;
+    const double tw = trace ? now() : 0;
     int r = finish(q, p.s, &n);
+    if (trace) t_wait += now() - tw;
     if (!r) {
       for (uint32_t i = 0; i < n; i++) match_ids[total + i] = p.base + p.s->h_result[1 + i];
       total += n;
@@ -738,6 +765,7 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
       rc = alloc_slot_outputs(q, *s, no + no / 4);
       if (rc) { release_slot(q, s); break; }
     }
+    const double tc = trace ? now() : 0;
     memcpy(s->h_tweaks, tweak_keys + (size_t)base * 64, (size_t)cnt * 64);
     if (out_offsets) {
       for (uint32_t i = 0; i <= cnt; i++) s->h_off[i] = out_offsets[base + i] - o0;
@@ -745,7 +773,9 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
     } else {
       memset(s->h_off, 0, ((size_t)cnt + 1) * 4);
     }
+    const double ts = trace ? now() : 0;
     rc = submit(q, s, cnt, no, 0);
+    if (trace) { t_copy += ts - tc; t_submit += now() - ts; }
     if (rc) { release_slot(q, s); break; }
     pending.push_back({s, base});
   }
@@ -756,6 +786,9 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
     if (!rc) rc = r;
   }
   *n_matches = total;
+  if (trace)
+    fprintf(stderr, "[cudasp] scan_batch %u rows: total %.3f ms, host copy %.3f, submit calls %.3f, waiting for the GPU %.3f\n", rows,
+            1e3 * (now() - t_begin), 1e3 * t_copy, 1e3 * t_submit, 1e3 * t_wait);
   return rc;
 }
 

@@ -62,7 +62,7 @@ int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_
                         const int *devices, int n_devices, uint32_t batch_rows,
                         uint64_t max_outputs_per_batch, cudasp_query **out);
 
-/* Same, with the number of staging slots per device chosen by the caller (0 = default 3; max 64).
+/* Same, with the number of staging slots per device chosen by the caller (0 = default 6; max 64).
  * A host with T producer threads (DuckDB workers, src/cudasp_extension.cu:516-532) wants about
  * T / n_devices + 2 so that no producer waits for a slot while batches are in flight. */
 int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64],
