@@ -41,6 +41,7 @@ struct Workspace {          // device-only scratch for one batch in flight
   fe *X = nullptr, *Y = nullptr, *Z = nullptr, *S = nullptr;   // rows each
   fe *D = nullptr, *DS = nullptr;                              // L * rows each (labels only)
   uint8_t *flags = nullptr;
+  uint8_t *invalid = nullptr;                                  // rows bytes: malformed compressed keys (KEYFMT 1)
   cudaEvent_t free_evt = nullptr;                              // recorded after the last kernel using it
   uint32_t cap_rows = 0;
   uint32_t cap_labels = 0;
@@ -145,6 +146,7 @@ int alloc_workspace(cudasp_query *q, Workspace &w, uint32_t rows, uint32_t L) {
   CU(q, cudaMalloc(&w.Y, n * sizeof(fe)));
   CU(q, cudaMalloc(&w.Z, n * sizeof(fe)));
   CU(q, cudaMalloc(&w.S, n * sizeof(fe)));
+  CU(q, cudaMalloc(&w.invalid, n));
   if (L) {
     CU(q, cudaMalloc(&w.D, n * L * sizeof(fe)));
     CU(q, cudaMalloc(&w.DS, n * L * sizeof(fe)));
@@ -154,7 +156,7 @@ int alloc_workspace(cudasp_query *q, Workspace &w, uint32_t rows, uint32_t L) {
   return 0;
 }
 void free_workspace(Workspace &w) {
-  cudaFree(w.X); cudaFree(w.Y); cudaFree(w.Z); cudaFree(w.S); cudaFree(w.D); cudaFree(w.DS); cudaFree(w.flags);
+  cudaFree(w.X); cudaFree(w.Y); cudaFree(w.Z); cudaFree(w.S); cudaFree(w.invalid); cudaFree(w.D); cudaFree(w.DS); cudaFree(w.flags);
   if (w.free_evt) cudaEventDestroy(w.free_evt);
   w = Workspace();
 }
@@ -265,29 +267,34 @@ int materialise_slot(cudasp_query *q, int di, Slot **out) {
 
 // K1 launch shapes.  Variant 0 is the production default; the others exist for tuning and are selected
 // with the environment variable CUDASP_LADDER_VARIANT (read once per process).
-template <int BLOCK, int MINB, int SYNC>
-void launch_ladder_t(const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp, cudaStream_t st) {
+template <int BLOCK, int MINB, int SYNC, int KEYFMT>
+void launch_ladder_t(const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp, uint8_t *invalid,
+                     cudaStream_t st) {
   static std::once_flag once;
   const int smem = LADDER_SMEM_WORDS_PER_THREAD * 4 * BLOCK;
   std::call_once(once, [&] {
-    cudaFuncSetAttribute(k_ladder<BLOCK, MINB, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(k_ladder<BLOCK, MINB, SYNC, KEYFMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   });
   const uint32_t grid = (rows + BLOCK - 1) / BLOCK;
-  k_ladder<BLOCK, MINB, SYNC><<<grid, BLOCK, smem, st>>>(d_tweaks, X, Y, Z, rows, lp);
+  k_ladder<BLOCK, MINB, SYNC, KEYFMT><<<grid, BLOCK, smem, st>>>(d_tweaks, X, Y, Z, rows, lp, invalid);
 }
+inline size_t key_bytes(int keyfmt) { return keyfmt == CUDASP_KEYS_SEC1_33 ? 33 : 64; }
 int ladder_variant() {
   static int v = [] { const char *e = getenv("CUDASP_LADDER_VARIANT"); return e ? atoi(e) : 0; }();
   return v;
 }
-void launch_ladder(int variant, const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp,
-                   cudaStream_t st) {
+void launch_ladder(int variant, int keyfmt, const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp,
+                   uint8_t *invalid, cudaStream_t st) {
+  if (keyfmt == CUDASP_KEYS_SEC1_33) {   // compressed keys: production shape only
+    launch_ladder_t<128, 4, 1, 1>(d_tweaks, X, Y, Z, rows, lp, invalid, st);
+    return;
+  }
   switch (variant) {
     default:
-    case 0: launch_ladder_t<128, 4, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;   // best measured (profiles/r01c)
-    case 1: launch_ladder_t<128, 3, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
-    case 2: launch_ladder_t<128, 4, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
-    case 3: launch_ladder_t<128, 3, 0>(d_tweaks, X, Y, Z, rows, lp, st); break;
-    case 4: launch_ladder_t<256, 2, 1>(d_tweaks, X, Y, Z, rows, lp, st); break;
+    case 0: launch_ladder_t<128, 4, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;   // best measured (profiles/r01c)
+    case 1: launch_ladder_t<128, 3, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
+    case 2: launch_ladder_t<128, 4, 0, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
+    case 3: launch_ladder_t<256, 2, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
   }
 }
 
@@ -295,7 +302,8 @@ void launch_ladder(int variant, const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, ui
 // d_result: [0] = match count (reset here), [1..] = ids.  Either may be NULL (candidate mode).
 int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_tweaks, const int64_t *d_outputs,
                     const uint32_t *d_off, uint32_t rows, uint32_t *d_ids, uint32_t *d_count, cudaStream_t st,
-                    int64_t *d_cands, uint8_t *dbg_S, uint8_t *dbg_t, uint8_t *dbg_P0, cudaEvent_t *stage_evs = nullptr) {
+                    int64_t *d_cands, uint8_t *dbg_S, uint8_t *dbg_t, uint8_t *dbg_P0, cudaEvent_t *stage_evs = nullptr,
+                    int keyfmt = CUDASP_KEYS_XY64) {
   // stage_evs (profiling entry only): 8 events recorded before each of the 7 possible kernels and
   // after the last one; a stage that does not run records its event anyway (zero duration).
   int ev_i = 0;
@@ -307,16 +315,22 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
   if (rows > w.cap_rows) return fail(q, CUDASP_ERR_ARG, "rows exceed the workspace capacity");
   const uint32_t L = q->n_labels;
   const host::QueryPlan &pl = q->plan;
+  const uint8_t *inv_flags = keyfmt == CUDASP_KEYS_SEC1_33 ? w.invalid : nullptr;
   uint64_t nl = 0;
   if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
   mark();
   if (!pl.fp.zero_scalar) {
-    launch_ladder(ladder_variant(), d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, st);
+    launch_ladder(ladder_variant(), keyfmt, d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, w.invalid, st);
     mark();
     const uint32_t T = inv_threads(rows);
     k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
     nl += 2;
   } else {
+    // scan key = 0 (mod n): S is the all-zero pair for every row; compressed keys are still validated (empty op list)
+    if (keyfmt == CUDASP_KEYS_SEC1_33) {
+      launch_ladder(ladder_variant(), keyfmt, d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, w.invalid, st);
+      nl += 1;
+    }
     mark();
   }
   mark();
@@ -329,7 +343,7 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
     mark();
     const uint32_t fgrid = (rows + FINAL_BLOCK - 1) / FINAL_BLOCK;
     k_final_base<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, d_outputs, d_off, dc.d_labels, L, w.D, w.flags,
-                                                            d_ids, d_count, d_cands, dbg_P0);
+                                                            d_ids, d_count, d_cands, dbg_P0, inv_flags);
     nl += 3;
     mark();
     if (L) {
@@ -339,7 +353,7 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
       k_batch_inv<<<(T2 + 127) / 128, 128, 0, st>>>(w.D, w.DS, n, T2);
       mark();
       k_final_labels<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.D, rows, d_outputs, d_off, dc.d_labels, L, w.flags,
-                                                                d_ids, d_count, d_cands);
+                                                                d_ids, d_count, d_cands, inv_flags);
       nl += 2;
     } else {
       mark();
@@ -568,7 +582,7 @@ void release_slot(cudasp_query *q, Slot *s) {
   q->cv.notify_all();
 }
 
-int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t tag) {
+int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t tag, int keyfmt = CUDASP_KEYS_XY64) {
   DevCtx &dc = q->devs[s->dev_index];
   CU(q, cudaSetDevice(dc.device));
   cudaStream_t st = s->stream;
@@ -577,14 +591,14 @@ int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t
   static const bool trace = getenv("CUDASP_TRACE") != nullptr;
   if (trace) cudaEventRecord(s->tr[0], st);
   if (rows) {
-    CU(q, cudaMemcpyAsync(s->d_tweaks, s->h_tweaks, (size_t)rows * 64, cudaMemcpyHostToDevice, st));
+    CU(q, cudaMemcpyAsync(s->d_tweaks, s->h_tweaks, (size_t)rows * key_bytes(keyfmt), cudaMemcpyHostToDevice, st));
     CU(q, cudaMemcpyAsync(s->d_off, s->h_off, ((size_t)rows + 1) * 4, cudaMemcpyHostToDevice, st));
     if (n_outputs) CU(q, cudaMemcpyAsync(s->d_outputs, s->h_outputs, n_outputs * 8, cudaMemcpyHostToDevice, st));
   }
   if (trace) cudaEventRecord(s->tr[1], st);
   CU(q, cudaStreamWaitEvent(st, s->ws.free_evt, 0));
   int rc = launch_pipeline(q, dc, s->ws, s->d_tweaks, s->d_outputs, s->d_off, rows, s->d_result + 1, s->d_result, st,
-                           nullptr, nullptr, nullptr, nullptr);
+                           nullptr, nullptr, nullptr, nullptr, nullptr, keyfmt);
   if (rc) return rc;
   if (trace) cudaEventRecord(s->tr[2], st);
   CU(q, cudaEventRecord(s->ws.free_evt, st));
@@ -656,13 +670,18 @@ int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot) {
 }
 
 int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag) {
+  return cudasp_submit_slot_fmt(q, slot, rows, n_outputs, tag, CUDASP_KEYS_XY64);
+}
+
+int cudasp_submit_slot_fmt(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag, int key_format) {
+  if (key_format != CUDASP_KEYS_XY64 && key_format != CUDASP_KEYS_SEC1_33) return fail(q, CUDASP_ERR_ARG, "unknown key format");
   if (!q || !slot) return fail(q, CUDASP_ERR_ARG, "bad slot");
   Slot *s = slot_by_id(q, slot->slot_id);
   if (!s) return fail(q, CUDASP_ERR_ARG, "bad slot");
   if (s->state != 1) return fail(q, CUDASP_ERR_STATE, "slot was not acquired");
   if (rows > s->cap_rows || n_outputs > s->cap_outputs) return fail(q, CUDASP_ERR_ARG, "rows/outputs exceed the slot capacity");
   if (rows && s->h_off[rows] != n_outputs) return fail(q, CUDASP_ERR_ARG, "out_offsets[rows] != n_outputs");
-  int rc = submit(q, s, rows, n_outputs, tag);
+  int rc = submit(q, s, rows, n_outputs, tag, key_format);
   if (rc) return rc;
   std::lock_guard<std::mutex> lk(q->mu);
   s->state = 2;
@@ -711,6 +730,13 @@ int cudasp_release_result(cudasp_query *q, const cudasp_result *r) {
 // ---- synchronous batch ----------------------------------------------------------------
 int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t *outputs, const uint32_t *out_offsets,
                       uint32_t rows, uint32_t *match_ids, uint32_t *n_matches) {
+  return cudasp_scan_batch_fmt(q, tweak_keys, CUDASP_KEYS_XY64, outputs, out_offsets, rows, match_ids, n_matches);
+}
+
+int cudasp_scan_batch_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                          const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches) {
+  if (key_format != CUDASP_KEYS_XY64 && key_format != CUDASP_KEYS_SEC1_33) return fail(q, CUDASP_ERR_ARG, "unknown key format");
+  const size_t kb = key_bytes(key_format);
   if (!q || !n_matches) return fail(q, CUDASP_ERR_ARG, "NULL argument");
   *n_matches = 0;
   if (rows == 0) return CUDASP_OK;
@@ -766,7 +792,7 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
       if (rc) { release_slot(q, s); break; }
     }
     const double tc = trace ? now() : 0;
-    memcpy(s->h_tweaks, tweak_keys + (size_t)base * 64, (size_t)cnt * 64);
+    memcpy(s->h_tweaks, tweak_keys + (size_t)base * kb, (size_t)cnt * kb);
     if (out_offsets) {
       for (uint32_t i = 0; i <= cnt; i++) s->h_off[i] = out_offsets[base + i] - o0;
       if (no) memcpy(s->h_outputs, outputs + o0, no * 8);
@@ -774,7 +800,7 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
       memset(s->h_off, 0, ((size_t)cnt + 1) * 4);
     }
     const double ts = trace ? now() : 0;
-    rc = submit(q, s, cnt, no, 0);
+    rc = submit(q, s, cnt, no, 0, key_format);
     if (trace) { t_copy += ts - tc; t_submit += now() - ts; }
     if (rc) { release_slot(q, s); break; }
     pending.push_back({s, base});
@@ -836,8 +862,9 @@ int cudasp_profile_stages(cudasp_query *q, int device, const uint8_t *d_tweak_ke
   Workspace &w = dc->slots[0]->ws;
   cudaStream_t st = dc->own_stream;
   CU(q, cudaStreamWaitEvent(st, w.free_evt, 0));
+  const char *kf = getenv("CUDASP_PROFILE_KEYFMT");      // tuning aid: "1" = d_tweak_keys holds 33-byte SEC1 keys
   int rc = launch_pipeline(q, *dc, w, d_tweak_keys, d_outputs, d_out_offsets, rows, d_match_ids, d_n_matches, st, nullptr, nullptr,
-                           nullptr, nullptr, ev);
+                           nullptr, nullptr, ev, kf && kf[0] == '1' ? CUDASP_KEYS_SEC1_33 : CUDASP_KEYS_XY64);
   if (!rc) {
     cudaEventRecord(w.free_evt, st);
     cudaError_t e = cudaStreamSynchronize(st);
@@ -850,9 +877,10 @@ int cudasp_profile_stages(cudasp_query *q, int device, const uint8_t *d_tweak_ke
 
 // ---- introspection --------------------------------------------------------------------
 static int scan_debug(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands, uint8_t *S_le, uint8_t *t_be,
-                      uint8_t *P0_le) {
+                      uint8_t *P0_le, int keyfmt = CUDASP_KEYS_XY64, uint8_t *valid = nullptr) {
   if (!q || (rows && !tweak_keys)) return fail(q, CUDASP_ERR_ARG, "NULL argument");
   const uint32_t L = q->n_labels;
+  const size_t kb = key_bytes(keyfmt);
   for (uint32_t base = 0; base < rows; base += q->batch_rows) {
     const uint32_t cnt = std::min<uint32_t>(q->batch_rows, rows - base);
     int rc = 0;
@@ -867,16 +895,22 @@ static int scan_debug(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows,
       if (S_le) CU(q, cudaMalloc(&d_S, (size_t)cnt * 64));
       if (t_be) CU(q, cudaMalloc(&d_t, (size_t)cnt * 32));
       if (P0_le) CU(q, cudaMalloc(&d_P, (size_t)cnt * 64));
-      CU(q, cudaMemcpyAsync(s->d_tweaks, tweak_keys + (size_t)base * 64, (size_t)cnt * 64, cudaMemcpyHostToDevice, s->stream));
+      CU(q, cudaMemcpyAsync(s->d_tweaks, tweak_keys + (size_t)base * kb, (size_t)cnt * kb, cudaMemcpyHostToDevice, s->stream));
       CU(q, cudaStreamWaitEvent(s->stream, s->ws.free_evt, 0));
-      int r = launch_pipeline(q, dc, s->ws, s->d_tweaks, nullptr, nullptr, cnt, nullptr, nullptr, s->stream, d_c, d_S, d_t, d_P);
+      int r = launch_pipeline(q, dc, s->ws, s->d_tweaks, nullptr, nullptr, cnt, nullptr, nullptr, s->stream, d_c, d_S, d_t, d_P, nullptr,
+                              keyfmt);
       if (r) return r;
       CU(q, cudaEventRecord(s->ws.free_evt, s->stream));
       if (cands) CU(q, cudaMemcpyAsync(cands + (size_t)base * (1 + L), d_c, (size_t)cnt * (1 + L) * 8, cudaMemcpyDeviceToHost, s->stream));
       if (S_le) CU(q, cudaMemcpyAsync(S_le + (size_t)base * 64, d_S, (size_t)cnt * 64, cudaMemcpyDeviceToHost, s->stream));
       if (t_be) CU(q, cudaMemcpyAsync(t_be + (size_t)base * 32, d_t, (size_t)cnt * 32, cudaMemcpyDeviceToHost, s->stream));
       if (P0_le) CU(q, cudaMemcpyAsync(P0_le + (size_t)base * 64, d_P, (size_t)cnt * 64, cudaMemcpyDeviceToHost, s->stream));
+      if (valid) {
+        if (keyfmt == CUDASP_KEYS_SEC1_33) CU(q, cudaMemcpyAsync(valid + base, s->ws.invalid, cnt, cudaMemcpyDeviceToHost, s->stream));
+        else memset(valid + base, 0, cnt);
+      }
       CU(q, cudaStreamSynchronize(s->stream));
+      if (valid) for (uint32_t i = 0; i < cnt; i++) valid[base + i] = valid[base + i] ? 0 : 1;   // invalid flag -> valid flag
       return 0;
     };
     rc = body();
@@ -889,6 +923,12 @@ static int scan_debug(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows,
 int cudasp_scan_candidates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands) {
   if (!cands) return fail(q, CUDASP_ERR_ARG, "NULL argument");
   return scan_debug(q, tweak_keys, rows, cands, nullptr, nullptr, nullptr);
+}
+int cudasp_scan_candidates_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, uint32_t rows, int64_t *cands,
+                               uint8_t *valid) {
+  if (!cands) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  if (key_format != CUDASP_KEYS_XY64 && key_format != CUDASP_KEYS_SEC1_33) return fail(q, CUDASP_ERR_ARG, "unknown key format");
+  return scan_debug(q, tweak_keys, rows, cands, nullptr, nullptr, nullptr, key_format, valid);
 }
 int cudasp_scan_intermediates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, uint8_t *S_le, uint8_t *t_be,
                               uint8_t *P0_le) {

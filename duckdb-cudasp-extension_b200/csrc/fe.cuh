@@ -498,4 +498,39 @@ CSP_HD void fe_inv(fe &r, const fe &a) {
   fe_mul(r, t, a);
 }
 
+
+// a^((p+1)/4): the square root of a when a is a quadratic residue (p = 3 mod 4); otherwise the square of the
+// result is -a.  (p+1)/4 = 2^254 - 2^30 - 244: blocks of ones of length 223, 22 and 2 -> 253 S + 13 M.
+// Used only to decompress 33-byte SEC1 tweak keys (reference CPU semantics: scripts/decompress_tweak_key.py:34-46).
+CSP_HD void fe_sqrt_candidate(fe &r, const fe &a) {
+  fe x2, x3, x6, x9, x11, x22, x44, x88, x176, x220, x223, t;
+  fe_sqr(x2, a);
+  fe_mul(x2, x2, a);
+  fe_sqr(x3, x2);
+  fe_mul(x3, x3, a);
+  fe_sqr_n<3>(x6, x3);
+  fe_mul(x6, x6, x3);
+  fe_sqr_n<3>(x9, x6);
+  fe_mul(x9, x9, x3);
+  fe_sqr_n<2>(x11, x9);
+  fe_mul(x11, x11, x2);
+  fe_sqr_n<11>(x22, x11);
+  fe_mul(x22, x22, x11);
+  fe_sqr_n<22>(x44, x22);
+  fe_mul(x44, x44, x22);
+  fe_sqr_n<44>(x88, x44);
+  fe_mul(x88, x88, x44);
+  fe_sqr_n<88>(x176, x88);
+  fe_mul(x176, x176, x88);
+  fe_sqr_n<44>(x220, x176);
+  fe_mul(x220, x220, x44);
+  fe_sqr_n<3>(x223, x220);
+  fe_mul(x223, x223, x3);
+  fe_sqr_n<23>(t, x223);
+  fe_mul(t, t, x22);
+  fe_sqr_n<6>(t, t);
+  fe_mul(t, t, x2);
+  fe_sqr_n<2>(r, t);
+}
+
 }  // namespace csp

@@ -27,10 +27,12 @@ struct SmemTab {
 };
 static const int LADDER_SMEM_WORDS_PER_THREAD = 4 * 3 * 8;
 
-template <int BLOCK, int MINB, int SYNC>
+// KEYFMT 0: 64-byte keys (x_LE || y_LE, the reference's layout).  KEYFMT 1: 33-byte SEC1 compressed keys,
+// decompressed here (decompress_tweak); `invalid[row]` then tells K5/K7 that the row can never match.
+template <int BLOCK, int MINB, int SYNC, int KEYFMT>
 __global__ void __launch_bounds__(BLOCK, MINB) k_ladder(const uint8_t *__restrict__ tweaks, fe *__restrict__ outX,
                                                         fe *__restrict__ outY, fe *__restrict__ outZ, uint32_t rows,
-                                                        const __grid_constant__ LadderParams prm) {
+                                                        const __grid_constant__ LadderParams prm, uint8_t *__restrict__ invalid) {
   extern __shared__ uint32_t smem_tab[];
   uint32_t row = blockIdx.x * BLOCK + threadIdx.x;
   const bool live = row < rows;
@@ -39,8 +41,17 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_ladder(const uint8_t *__restric
   SmemTab<BLOCK> tab;
   tab.base = smem_tab + threadIdx.x;
   ge P;
-  load_fe_ro(P.x, reinterpret_cast<const fe *>(tweaks + (size_t)row * 64));
-  load_fe_ro(P.y, reinterpret_cast<const fe *>(tweaks + (size_t)row * 64 + 32));
+  if (KEYFMT == 0) {
+    load_fe_ro(P.x, reinterpret_cast<const fe *>(tweaks + (size_t)row * 64));
+    load_fe_ro(P.y, reinterpret_cast<const fe *>(tweaks + (size_t)row * 64 + 32));
+  } else {
+    uint8_t sec1[33];
+    const uint8_t *src = tweaks + (size_t)row * 33;
+#pragma unroll
+    for (int i = 0; i < 33; i++) sec1[i] = __ldg(src + i);
+    const bool ok = decompress_tweak(P, sec1);
+    if (live) invalid[row] = ok ? 0 : 1;
+  }
   gej acc;
   ladder_row<SmemTab<BLOCK>, SYNC>(acc, P, prm, tab);
   if (!live) return;
@@ -114,7 +125,8 @@ __global__ void __launch_bounds__(BLOCK) k_final_base(fe *__restrict__ X, fe *__
                                                       const uint32_t *__restrict__ out_off, const ge *__restrict__ labels,
                                                       uint32_t n_labels, fe *__restrict__ D, uint8_t *__restrict__ flags,
                                                       uint32_t *__restrict__ match_ids, uint32_t *__restrict__ n_matches,
-                                                      int64_t *__restrict__ cands_out, uint8_t *__restrict__ dbg_P0) {
+                                                      int64_t *__restrict__ cands_out, uint8_t *__restrict__ dbg_P0,
+                                                      const uint8_t *__restrict__ invalid) {
   const uint32_t row = blockIdx.x * BLOCK + threadIdx.x;   // grid is a whole number of warps
   const bool live = row < rows;
   bool hit = false;
@@ -127,6 +139,7 @@ __global__ void __launch_bounds__(BLOCK) k_final_base(fe *__restrict__ X, fe *__
     const int64_t cand = base_candidate(x0, need_y ? &y0 : nullptr, X1, Y1, zi);
     if (cands_out) cands_out[(size_t)row * (1 + n_labels)] = cand;
     if (outputs) hit = outputs_contain(outputs, out_off[row], out_off[row + 1], cand);
+    if (invalid && invalid[row]) hit = false;      // malformed compressed key: never matches
     if (need_y) {
       store_fe(X + row, x0);
       store_fe(Y + row, y0);
@@ -154,7 +167,8 @@ __global__ void __launch_bounds__(BLOCK) k_final_labels(const fe *__restrict__ X
                                                         const int64_t *__restrict__ outputs, const uint32_t *__restrict__ out_off,
                                                         const ge *__restrict__ labels, uint32_t n_labels,
                                                         const uint8_t *__restrict__ flags, uint32_t *__restrict__ match_ids,
-                                                        uint32_t *__restrict__ n_matches, int64_t *__restrict__ cands_out) {
+                                                        uint32_t *__restrict__ n_matches, int64_t *__restrict__ cands_out,
+                                                        const uint8_t *__restrict__ invalid) {
   const uint32_t row = blockIdx.x * BLOCK + threadIdx.x;
   const bool live = row < rows;
   bool hit = false;
@@ -173,6 +187,7 @@ __global__ void __launch_bounds__(BLOCK) k_final_labels(const fe *__restrict__ X
       if (cands_out) cands_out[(size_t)row * (1 + n_labels) + 1 + i] = cand;
       if (outputs) hit |= outputs_contain(outputs, lo, hi, cand);
     }
+    if (invalid && invalid[row]) hit = false;
   }
   if (match_ids) append_match(live && hit, row, match_ids, n_matches);
 }

@@ -71,6 +71,45 @@ CSP_HD void store_fe(fe *p, const fe &r) {
 #endif
 }
 
+// ---------------------------------------------------------------- compressed tweak keys
+// 33-byte SEC1: prefix 02 / 03 (parity of y) || x big-endian.  Same result as the reference's CPU recipe
+// (scripts/decompress_tweak_key.py:26-46): y = (x^3 + 7)^((p+1)/4), negated when its parity differs from the prefix.
+// Returns false -- the row can never match -- for a bad prefix, x >= p, or x not on the curve.
+CSP_HD bool decompress_tweak(ge &P, const uint8_t *sec1) {
+  const uint32_t prefix = sec1[0];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int l = 0; l < 8; l++) {
+    const uint8_t *b = sec1 + 1 + 4 * (7 - l);
+    P.x.v[l] = ((uint32_t)b[0] << 24) | ((uint32_t)b[1] << 16) | ((uint32_t)b[2] << 8) | (uint32_t)b[3];
+  }
+  fe xc = P.x;
+  fe_normalize(xc);
+  bool ok = (prefix == 2u || prefix == 3u);
+  bool canonical = true;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int l = 0; l < 8; l++) canonical &= (xc.v[l] == P.x.v[l]);      // x >= p is not a valid encoding
+  ok &= canonical;
+  fe y2, seven, y, chk;
+  fe_sqr(y2, P.x);
+  fe_mul(y2, y2, P.x);
+  fe_set_u32(seven, 7);
+  fe_add(y2, y2, seven);
+  fe_sqrt_candidate(y, y2);
+  fe_sqr(chk, y);
+  ok &= fe_equal(chk, y2);
+  fe_normalize(y);
+  if ((y.v[0] & 1u) != (prefix & 1u)) {
+    fe_neg(y, y);
+    fe_normalize(y);
+  }
+  P.y = y;
+  return ok;
+}
+
 // ---------------------------------------------------------------- K1 body: S = scan_sk * P
 // Tab: storage for the 4-entry odd-multiples table, components 0 = x, 1 = beta*x, 2 = y;
 //      needs  uint32_t get(e, c, l)  and  void set(e, c, l, v).

@@ -32,6 +32,7 @@ namespace {
 
 constexpr idx_t SCALAR_SIZE = 32;      // scan_private_key: 32 B little-endian
 constexpr idx_t POINT_SIZE = 64;       // x_LE || y_LE
+constexpr idx_t SEC1_SIZE = 33;        // (02|03) || x_BE: the index's own storage format, decompressed on the GPU
 constexpr idx_t DEFAULT_BATCH = 300000;  // reference default (:473)
 constexpr idx_t MAX_BATCH = 10000000;
 
@@ -49,6 +50,7 @@ struct InFlightBatch {
 	vector<uint32_t> txid_end;   // txid i = txid_bytes[txid_end[i-1] .. txid_end[i])
 	vector<int32_t> heights;
 	const uint8_t *tweak_keys = nullptr;  // the slot's pinned buffer: valid until the result is released
+	uint32_t key_bytes = 64;              // one key format per batch (CUDASP_KEYS_XY64 / CUDASP_KEYS_SEC1_33)
 };
 
 struct CudaspScanState : public GlobalTableFunctionState {
@@ -87,6 +89,7 @@ struct CudaspScanLocalState : public LocalTableFunctionState {
 	cudasp_slot slot;
 	uint32_t rows = 0;
 	uint64_t n_outputs = 0;
+	uint32_t key_bytes = 64;   // key format of the batch being filled
 	unique_ptr<InFlightBatch> meta;
 };
 
@@ -243,7 +246,7 @@ static void CollectResult(CudaspScanState &state, const cudasp_result &r) {
 			const uint32_t b = i ? meta->txid_end[i - 1] : 0, e = meta->txid_end[i];
 			state.output_txids.emplace_back(meta->txid_bytes.data() + b, e - b);
 			state.output_heights.push_back(meta->heights[i]);
-			state.output_tweak_keys.emplace_back(const_char_ptr_cast(meta->tweak_keys) + (size_t)i * POINT_SIZE, POINT_SIZE);
+			state.output_tweak_keys.emplace_back(const_char_ptr_cast(meta->tweak_keys) + (size_t)i * meta->key_bytes, meta->key_bytes);
 		}
 	}
 	if (cudasp_release_result(state.query, &r) != CUDASP_OK) {
@@ -313,7 +316,8 @@ static void SubmitSlot(CudaspScanState &state, CudaspScanLocalState &local) {
 		std::lock_guard<std::mutex> guard(state.inflight_lock);
 		state.inflight[tag] = std::move(local.meta);
 	}
-	if (cudasp_submit_slot(state.query, &local.slot, local.rows, local.n_outputs, tag) != CUDASP_OK) {
+	const int fmt = local.key_bytes == SEC1_SIZE ? CUDASP_KEYS_SEC1_33 : CUDASP_KEYS_XY64;
+	if (cudasp_submit_slot_fmt(state.query, &local.slot, local.rows, local.n_outputs, tag, fmt) != CUDASP_OK) {
 		ThrowGpu(state, "cudasp_submit_slot");
 	}
 	local.have_slot = false;
@@ -324,7 +328,9 @@ static void SubmitSlot(CudaspScanState &state, CudaspScanLocalState &local) {
 // ------------------------------------------------------------------------------------------ execute
 // One DataChunk (<= 2048 rows) -> pinned staging.  Row rules are the reference's AccumulateInput (:154-224):
 // a row with NULL txid, height or tweak_key is dropped; a NULL outputs list is an empty list; NULL list children
-// are skipped.  A tweak_key that is not 64 bytes can never match (the reference reads out of bounds): dropped.
+// are skipped.  tweak_key: 64 bytes (the reference's format) or 33 bytes (compressed SEC1, decompressed in K1); a
+// batch holds one format, so a change of key length cuts the batch.  Any other length can never match (the reference
+// reads out of bounds there): dropped.
 static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local, const CudaspScanBindData &bind,
                             DataChunk &input) {
 	if (input.ColumnCount() < 4) {
@@ -356,8 +362,12 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 			continue;
 		}
 		const string_t &tw = tweaks[wi];
-		if (tw.GetSize() != POINT_SIZE) {
+		const idx_t key_size = tw.GetSize();
+		if (key_size != POINT_SIZE && key_size != SEC1_SIZE) {
 			continue;
+		}
+		if (local.have_slot && local.rows && local.key_bytes != key_size) {
+			SubmitSlot(state, local);
 		}
 		const idx_t li = list_f.sel->get_index(r);
 		const bool has_list = list_f.validity.RowIsValid(li);
@@ -373,7 +383,10 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 			                            (uint64_t)list_len, (uint64_t)local.slot.cap_outputs);
 		}
 		const uint32_t row = local.rows;
-		memcpy(local.slot.tweak_keys + (size_t)row * POINT_SIZE, tw.GetData(), POINT_SIZE);
+		if (row == 0) {
+			local.key_bytes = local.meta->key_bytes = (uint32_t)key_size;
+		}
+		memcpy(local.slot.tweak_keys + (size_t)row * key_size, tw.GetData(), key_size);
 		uint64_t n_out = local.n_outputs;
 		if (has_list) {
 			const idx_t off = lists[li].offset;

@@ -1,2 +1,2 @@
-from .binding import CudaspError, Query, lib, test_field, LIB_PATH, EXPORTS, profile_stages, STAGES  # noqa: F401
+from .binding import CudaspError, Query, lib, test_field, LIB_PATH, EXPORTS, profile_stages, STAGES, KEYS_XY64, KEYS_SEC1_33  # noqa: F401
 from .table_function import (CudaspScanBind, InvalidInputException, IOException, cudasp_scan)  # noqa: F401

@@ -30,10 +30,14 @@ class Result(C.Structure):
                 ("match_ids", u32p)]
 
 
+KEYS_XY64, KEYS_SEC1_33 = 0, 1          # include/cudasp.h CUDASP_KEYS_*
+KEY_BYTES = {KEYS_XY64: 64, KEYS_SEC1_33: 33}
+
 EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "cudasp_query_destroy", "cudasp_scan_batch",
            "cudasp_acquire_slot", "cudasp_submit_slot", "cudasp_poll", "cudasp_wait", "cudasp_release_result",
            "cudasp_scan_device", "cudasp_profile_stages", "cudasp_scan_candidates", "cudasp_scan_intermediates", "cudasp_test_field",
-           "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory"]
+           "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory",
+           "cudasp_scan_batch_fmt", "cudasp_submit_slot_fmt", "cudasp_scan_candidates_fmt"]
 
 
 def lib():
@@ -59,6 +63,9 @@ def lib():
         L.cudasp_scan_device.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, vp, vp]
         L.cudasp_profile_stages.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, vp, C.POINTER(C.c_float)]
         L.cudasp_scan_candidates.argtypes = [vp, vp, C.c_uint32, vp]
+        L.cudasp_scan_batch_fmt.argtypes = [vp, vp, C.c_int, vp, vp, C.c_uint32, vp, u32p]
+        L.cudasp_submit_slot_fmt.argtypes = [vp, C.POINTER(Slot), C.c_uint32, C.c_uint64, C.c_uint64, C.c_int]
+        L.cudasp_scan_candidates_fmt.argtypes = [vp, vp, C.c_int, C.c_uint32, vp, vp]
         L.cudasp_scan_intermediates.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
         L.cudasp_test_field.argtypes = [C.c_int, C.c_int, vp, vp, vp, C.c_uint32]
         L.cudasp_launch_count.argtypes = [vp]
@@ -132,9 +139,11 @@ class Query:
     def launch_count(self) -> int:
         return int(lib().cudasp_launch_count(self._h))
 
-    def scan_batch(self, tweaks: np.ndarray, outputs: Optional[np.ndarray], out_offsets: Optional[np.ndarray]) -> np.ndarray:
-        """tweaks uint8 [rows,64]; outputs int64 [n]; out_offsets uint32 [rows+1] -> ascending matching row ids."""
-        tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, 64)
+    def scan_batch(self, tweaks: np.ndarray, outputs: Optional[np.ndarray], out_offsets: Optional[np.ndarray],
+                   key_format: int = KEYS_XY64) -> np.ndarray:
+        """tweaks uint8 [rows,64] (or [rows,33] with key_format=KEYS_SEC1_33); outputs int64 [n]; out_offsets uint32
+        [rows+1] -> ascending matching row ids."""
+        tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, KEY_BYTES[key_format])
         rows = tweaks.shape[0]
         if out_offsets is not None:
             out_offsets = np.ascontiguousarray(out_offsets, dtype=np.uint32)
@@ -142,16 +151,24 @@ class Query:
             outputs = np.ascontiguousarray(outputs if outputs is not None else np.zeros(0, np.int64), dtype=np.int64)
         ids = np.zeros(max(rows, 1), np.uint32)
         n = C.c_uint32(0)
-        self._check(lib().cudasp_scan_batch(self._h, _ptr(tweaks), _ptr(outputs) if out_offsets is not None else None,
-                                            _ptr(out_offsets), rows, _ptr(ids), C.byref(n)))
+        outp = _ptr(outputs) if out_offsets is not None else None
+        if key_format == KEYS_XY64:     # the reference-shaped entry point
+            self._check(lib().cudasp_scan_batch(self._h, _ptr(tweaks), outp, _ptr(out_offsets), rows, _ptr(ids), C.byref(n)))
+        else:
+            self._check(lib().cudasp_scan_batch_fmt(self._h, _ptr(tweaks), key_format, outp, _ptr(out_offsets), rows, _ptr(ids),
+                                                    C.byref(n)))
         return ids[: n.value].copy()
 
-    def candidates(self, tweaks: np.ndarray) -> np.ndarray:
-        tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, 64)
+    def candidates(self, tweaks: np.ndarray, key_format: int = KEYS_XY64, with_valid: bool = False):
+        tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, KEY_BYTES[key_format])
         rows = tweaks.shape[0]
         out = np.zeros((max(rows, 1), 1 + self.n_labels), np.int64)
-        self._check(lib().cudasp_scan_candidates(self._h, _ptr(tweaks), rows, _ptr(out)))
-        return out[:rows]
+        if key_format == KEYS_XY64 and not with_valid:
+            self._check(lib().cudasp_scan_candidates(self._h, _ptr(tweaks), rows, _ptr(out)))
+            return out[:rows]
+        valid = np.zeros(max(rows, 1), np.uint8)
+        self._check(lib().cudasp_scan_candidates_fmt(self._h, _ptr(tweaks), key_format, rows, _ptr(out), _ptr(valid)))
+        return (out[:rows], valid[:rows].astype(bool)) if with_valid else out[:rows]
 
     def intermediates(self, tweaks: np.ndarray):
         tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, 64)

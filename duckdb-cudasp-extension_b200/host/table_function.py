@@ -16,9 +16,10 @@ from typing import Iterable, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from .binding import CudaspError, Query
+from .binding import KEYS_SEC1_33, KEYS_XY64, CudaspError, Query
 
 TWEAK_KEY_SIZE = 64   # CudaspScanBindData::TWEAK_KEY_SIZE  (src/cudasp_extension.cu:90)
+COMPRESSED_KEY_SIZE = 33   # extension: SEC1 keys as the index stores them, decompressed on the GPU
 SCALAR_SIZE = 32      # CudaspScanBindData::SCALAR_SIZE     (:91)
 STANDARD_VECTOR_SIZE = 2048
 
@@ -126,22 +127,30 @@ def ProcessBatch(local_state: CudaspScanLocalState, bind_data: CudaspScanBindDat
     n = len(local_state.accumulated_txids)
     if n == 0:
         return
-    # a tweak_key that is not 64 bytes can never match (the reference reads out of bounds): give it an
-    # all-zero point and mask the row afterwards
-    bad = [i for i, t in enumerate(local_state.accumulated_tweak_keys) if len(t) != TWEAK_KEY_SIZE]
-    tw = np.zeros((n, 64), np.uint8)
-    good = [t if len(t) == TWEAK_KEY_SIZE else b"\0" * 64 for t in local_state.accumulated_tweak_keys]
-    tw[:] = np.frombuffer(b"".join(good), np.uint8).reshape(n, 64)
-    outputs = np.array(local_state.accumulated_outputs, dtype=np.int64)
-    offsets = np.array(local_state.accumulated_output_offsets, dtype=np.uint32)
-    try:
-        ids = global_state.query.scan_batch(tw, outputs, offsets)
-    except CudaspError as e:
-        raise IOException(str(e))
-    badset = set(bad)
-    for i in ids.tolist():
-        if i in badset:
+    # rows are scanned per key format: 64-byte keys the reference's way, 33-byte SEC1 keys decompressed on the
+    # GPU (what scripts/decompress_tweak_key.py does on the CPU before the table is loaded); a tweak_key of any
+    # other length can never match (the reference reads out of bounds there) and is skipped
+    offs = np.array(local_state.accumulated_output_offsets, dtype=np.int64)
+    outs = np.array(local_state.accumulated_outputs, dtype=np.int64)
+    lens = np.fromiter((len(t) for t in local_state.accumulated_tweak_keys), dtype=np.int64, count=n)
+    matched: List[int] = []
+    for size, fmt in ((TWEAK_KEY_SIZE, KEYS_XY64), (COMPRESSED_KEY_SIZE, KEYS_SEC1_33)):
+        sel = np.nonzero(lens == size)[0]
+        if len(sel) == 0:
             continue
+        tw = np.frombuffer(b"".join(local_state.accumulated_tweak_keys[i] for i in sel), np.uint8).reshape(len(sel), size)
+        if len(sel) == n:
+            sub_out, sub_off = outs, offs
+        else:
+            cnt = offs[sel + 1] - offs[sel]
+            sub_off = np.concatenate([[0], np.cumsum(cnt)])
+            sub_out = np.concatenate([outs[offs[i]: offs[i + 1]] for i in sel]) if len(sel) else outs[:0]
+        try:
+            ids = global_state.query.scan_batch(tw, sub_out, sub_off.astype(np.uint32), key_format=fmt)
+        except CudaspError as e:
+            raise IOException(str(e))
+        matched.extend(int(sel[i]) for i in ids.tolist())
+    for i in sorted(matched):
         global_state.output_txids.append(local_state.accumulated_txids[i])
         global_state.output_heights.append(local_state.accumulated_heights[i])
         global_state.output_tweak_keys.append(local_state.accumulated_tweak_keys[i])

@@ -36,6 +36,13 @@ extern "C" {
 #define CUDASP_ERR_STATE (-3)  /* call not valid in this state (e.g. slot not acquired) */
 #define CUDASP_ERR_KEY (-4)    /* scan key for which no valid ladder schedule exists */
 
+/* Tweak-key formats.  XY64 is the reference's (64 B = x_LE || y_LE).  SEC1_33 is this build's extension:
+ * 33-byte compressed SEC1 keys (02/03 || x big-endian), decompressed on the GPU with the reference's CPU recipe
+ * (scripts/decompress_tweak_key.py:26-46); a malformed key (bad prefix, x >= p, x not on the curve) never matches.
+ * In a staging slot compressed keys are packed at 33 bytes per row from the start of slot.tweak_keys. */
+#define CUDASP_KEYS_XY64 0
+#define CUDASP_KEYS_SEC1_33 1
+
 #define CUDASP_MAX_LABELS 64u
 #define CUDASP_MAX_BATCH_ROWS 10000000u /* reference: batch_size <= 10,000,000 (src/cudasp_extension.cu:485) */
 
@@ -85,6 +92,10 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys /* rows * 64 B 
                       const int64_t *outputs, const uint32_t *out_offsets /* rows + 1 */,
                       uint32_t rows, uint32_t *match_ids, uint32_t *n_matches);
 
+/* Same with an explicit key format (CUDASP_KEYS_*); tweak_keys holds rows * 33 bytes for SEC1_33. */
+int cudasp_scan_batch_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                          const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches);
+
 /* ---- streaming: pinned double-buffered staging, async H2D on per-device streams -------------
  * The host fills a pinned slot directly from its column vectors (what AccumulateInput does into
  * std::vectors, src/cudasp_extension.cu:154-224), submits it, and collects results later. */
@@ -112,6 +123,8 @@ int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot);
 int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot);
 /* Enqueue H2D + kernels + D2H for `rows` rows / `n_outputs` outputs of an acquired slot. */
 int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag);
+int cudasp_submit_slot_fmt(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag,
+                           int key_format);
 /* Returns 1 and fills *r when a finished batch is available, 0 when none is finished yet. */
 int cudasp_poll(cudasp_query *q, cudasp_result *r);
 /* Blocks for the oldest in-flight batch; returns 1 with *r filled, or 0 when nothing is in flight. */
@@ -137,6 +150,9 @@ int cudasp_profile_stages(cudasp_query *q, int device, const uint8_t *d_tweak_ke
 /* ---- introspection used by the parity tests and bench.py -----------------------------------
  * Per-row candidates instead of match flags: cands[r*(1+L) + 0] = base, [.. + 1 + i] = label i. */
 int cudasp_scan_candidates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands);
+/* Same for either key format; valid[r] (optional) = 1 unless row r's compressed key is malformed. */
+int cudasp_scan_candidates_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, uint32_t rows, int64_t *cands,
+                               uint8_t *valid);
 /* Per-row intermediates: shared secret S (64 B LE x||y), t (32 B big-endian), P0 (64 B LE). Any may be NULL. */
 int cudasp_scan_intermediates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows,
                               uint8_t *S_le, uint8_t *t_be, uint8_t *P0_le);

@@ -111,6 +111,13 @@ def gtab_entry(w, d):
     return out.tobytes()
 
 
+def decompress(sec1: bytes):
+    lib = load()
+    out = np.zeros(64, np.uint8)
+    ok = lib.hc_decompress(_p(_b(sec1)), _p(out))
+    return bool(ok), out.tobytes()
+
+
 def gtab_shape():
     lib = load()
     a, b = C.c_int(), C.c_int()

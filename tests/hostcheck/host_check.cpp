@@ -170,6 +170,13 @@ void hc_gtab_entry(int w, int d, uint8_t out[64]) {
   fe_to_le_bytes(out, e.x); fe_to_le_bytes(out + 32, e.y);
 }
 void hc_gtab_offset(int w, uint8_t out[32]) { gtab_offset(w).to_le(out, 32); }
+// 33-byte SEC1 -> 64 B LE x||y; returns 1 when valid
+int hc_decompress(const uint8_t sec1[33], uint8_t out[64]) {
+  ge P;
+  bool ok = decompress_tweak(P, sec1);
+  fe_to_le_bytes(out, P.x); fe_to_le_bytes(out + 32, P.y);
+  return ok ? 1 : 0;
+}
 void hc_gtab_shape(int *wbits, int *nwin) { *wbits = GTAB_WBITS; *nwin = GTAB_NWIN; }
 uint32_t hc_gtab_digit(const uint8_t t_le[32], int w) { fe t; fe_from_le_bytes(t, t_le); return gtab_digit(t, w); }
 }

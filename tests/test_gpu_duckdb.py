@@ -114,3 +114,42 @@ def test_synthetic_table_through_duckdb(tmp_path, threads, batch):
     want = sorted((txids[i].hex().upper(), heights[i], tweaks[i].hex().upper()) for i in expected)
     got = sorted((a, int(b), c) for a, b, c in (ln.split(",") for ln in lines))
     assert got == want
+
+
+@pytest.mark.parametrize("mode,threads", [("compressed", 8), ("mixed", 4)])
+def test_compressed_tweak_keys_through_duckdb(tmp_path, mode, threads):
+    """33-byte SEC1 tweak keys (the index's storage format) scanned directly; 'mixed' alternates runs of both key
+    lengths (each change cuts a batch) and sprinkles malformed keys that must never match."""
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    from tests.test_gpu_compressed import compress
+    rows, L, batch = 30000, 1, 4096
+    T = synth.make_table(rows, 6060, n_labels=L, n_base=40, n_per_label=10, batch_rows=batch, specials=False)
+    off = T["offsets"].astype(np.int64)
+    outs = [T["outputs"][off[i]:off[i + 1]].tolist() for i in range(rows)]
+    ck = compress(T["tweaks"])
+    expected = set(int(x) for x in T["expected"])
+    tweaks = []
+    for i in range(rows):
+        use33 = mode == "compressed" or (i // 777) % 2 == 0
+        tweaks.append(ck[i].tobytes() if use33 else T["tweaks"][i].tobytes())
+    if mode == "mixed":
+        for k, i in enumerate(sorted(expected)[:6]):
+            if len(tweaks[i]) == 33:
+                tweaks[i] = (b"\x04" if k % 2 else b"\x00") + tweaks[i][1:]       # bad prefix
+            else:
+                tweaks[i] = tweaks[i][:63]                                        # neither length
+            expected.discard(i)
+    txids = [i.to_bytes(4, "little") * 8 for i in range(rows)]
+    heights = [800000 + i // 3000 for i in range(rows)]
+    tbl = pa.table({"txid": pa.array(txids, pa.binary()), "height": pa.array(heights, pa.int32()),
+                    "tweak_key": pa.array(tweaks, pa.binary()), "outputs": pa.array(outs, pa.list_(pa.int64()))})
+    path = str(tmp_path / "c.parquet")
+    pq.write_table(tbl, path, row_group_size=5000)
+    q = dict(scan_sk=T["sk"].hex(), spend=T["spend"].hex(), labels=[l.hex() for l in T["labels"]], batch_size=batch)
+    sql = "SELECT hex(txid), height, hex(tweak_key) FROM %s ORDER BY 1;" % scan_call("read_parquet('%s')" % path, q)
+    rc, lines, err = run_sql(sql, threads=threads)
+    assert rc == 0, err
+    want = sorted((txids[i].hex().upper(), heights[i], tweaks[i].hex().upper()) for i in expected)
+    got = sorted((a, int(b), c) for a, b, c in (ln.split(",") for ln in lines))
+    assert got == want

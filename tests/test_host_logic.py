@@ -176,3 +176,35 @@ def test_label_edge_cases_and_zero_scalar():
     for k in (0, N):
         z = R.row_intermediates(0, R.parse_point(tw), R.G)
         assert H.scan_candidates(k.to_bytes(32, "little"), spend, [], [tw])[0].tolist() == z["cands"]
+
+
+def test_decompress_tweak_row_function():
+    """33-byte SEC1 keys: the device row function vs the oracle's restatement of
+    scripts/decompress_tweak_key.py, including the reference's own example and malformed keys."""
+    ref = bytes.fromhex("024ac253c216532e961988e2a8ce266a447c894c781e52ef6cee902361db960004")   # decompress_tweak_key.py:19
+    ok, out = H.decompress(ref)
+    assert ok and R.parse_point(out) == R.decompress_sec1(ref)
+    assert R.on_curve(R.parse_point(out))
+    rng = random.Random(33)
+    n_ok = n_bad = 0
+    for i in range(60):
+        x = rng.randrange(P)
+        for prefix in (2, 3):
+            blob = bytes([prefix]) + x.to_bytes(32, "big")
+            want = R.decompress_sec1(blob)
+            ok, out = H.decompress(blob)
+            assert ok == (want is not None)
+            if want is not None:
+                assert R.parse_point(out) == want and (want[1] & 1) == (prefix & 1)
+                n_ok += 1
+            else:
+                n_bad += 1
+    assert n_ok > 20 and n_bad > 20
+    g = R.G
+    for blob, valid in [(bytes([2 + (g[1] & 1)]) + g[0].to_bytes(32, "big"), True), (bytes([4]) + g[0].to_bytes(32, "big"), False),
+                        (bytes([0]) + g[0].to_bytes(32, "big"), False), (bytes([2]) + (P + 1).to_bytes(32, "big"), False),
+                        (bytes([3]) + P.to_bytes(32, "big"), False)]:
+        ok, out = H.decompress(blob)
+        assert ok == valid == (R.decompress_sec1(blob) is not None)
+        if valid:
+            assert R.parse_point(out) == g

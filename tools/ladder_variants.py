@@ -23,6 +23,11 @@ def child():
     L = int(os.environ.get("LABELS", "0"))
     T = synth.make_table(rows, 352002, n_labels=L, n_base=100, n_per_label=20 if L else 0, batch_rows=rows)
     q = M.Query(T["sk"], T["spend"], T["labels"], devices=[0], batch_rows=rows, max_outputs_per_batch=int(T["offsets"][-1]) + 16)
+    fmt = int(os.environ.get("KEYFMT", "0"))     # 1: 33-byte SEC1 keys
+    if fmt:
+        from tests.test_gpu_compressed import compress
+        os.environ["CUDASP_PROFILE_KEYFMT"] = "1"
+        T["tweaks"] = compress(T["tweaks"])
     d_tw = torch.from_numpy(T["tweaks"]).cuda()
     d_out = torch.from_numpy(T["outputs"]).cuda()
     d_off = torch.from_numpy(T["offsets"].astype(np.int64)).to(torch.int32).cuda()
@@ -36,7 +41,7 @@ def child():
     got = np.sort(ids[: int(n.item())].cpu().numpy().astype(np.uint32))
     ok = bool(np.array_equal(got, T["expected"]))
     tot = sum(best.values())
-    print(json.dumps({"variant": os.environ.get("CUDASP_LADDER_VARIANT", "0"), "ok": ok, "rows": rows, "total_ms": round(tot, 4),
+    print(json.dumps({"variant": os.environ.get("CUDASP_LADDER_VARIANT", "0"), "keyfmt": fmt, "ok": ok, "rows": rows, "total_ms": round(tot, 4),
                       "Mrows_s": round(rows / tot / 1e3, 2), **{k: round(v, 4) for k, v in best.items()}}))
     q.close()
 
@@ -45,7 +50,7 @@ if __name__ == "__main__":
     if os.environ.get("_LV_CHILD"):
         child()
     else:
-        variants = sys.argv[1:] or ["0", "1", "2", "3", "4"]
+        variants = sys.argv[1:] or ["0", "1", "2", "3"]
         for v in variants:
             env = dict(os.environ, CUDASP_LADDER_VARIANT=v, _LV_CHILD="1")
             p = subprocess.run([sys.executable, os.path.abspath(__file__)], env=env, capture_output=True, text=True, timeout=300)
