@@ -1,0 +1,439 @@
+// Arrow C-data-interface front-end of the cudasp_scan hot path (include/cudasp_arrow.h): host-only code that fills the
+// pinned staging slots of the C-ABI core straight from Arrow buffers.  Replaces, for columnar callers, the reference's
+// per-row AccumulateInput + ProcessBatch marshalling (/root/reference/src/cudasp_extension.cu:154-330).
+//
+// Two staging paths per piece (a piece = up to piece_rows rows, whole K1 waves):
+//   dense   : no NULL keys / lists / children in sight and one key width -> memcpy(keys), rebase(offsets), memcpy(values)
+//   general : row by row with the reference's NULL rules, rows compacted, a row map kept to translate ids back
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <string>
+#include <vector>
+
+#include "../../include/cudasp_arrow.h"
+#include "staging_internal.hpp"
+
+namespace {
+
+using csp::staging::Staging;
+namespace stg = csp::staging;
+
+inline bool bit_set(const uint8_t *bits, int64_t i) { return (bits[i >> 3] >> (i & 7)) & 1; }
+
+struct KeyColumn {
+  int width = 0;                    // > 0: fixed_size_binary(width); 0: variable (offsets)
+  bool large = false;               // variable: 64-bit offsets
+  const uint8_t *validity = nullptr;
+  const void *offsets = nullptr;
+  const uint8_t *data = nullptr;
+  int64_t offset = 0, length = 0;
+  bool may_have_nulls = false;
+
+  bool valid(int64_t i) const { return !validity || bit_set(validity, offset + i); }
+  int64_t begin(int64_t i) const {
+    if (width) return (offset + i) * width;
+    return large ? static_cast<const int64_t *>(offsets)[offset + i] : static_cast<const int32_t *>(offsets)[offset + i];
+  }
+  int64_t size(int64_t i) const { return width ? width : begin(i + 1) - begin(i); }
+};
+
+struct ListColumn {
+  bool large = false;
+  const uint8_t *validity = nullptr;
+  const void *offsets = nullptr;
+  int64_t offset = 0, length = 0;
+  bool may_have_nulls = false;
+  // child
+  const uint8_t *child_validity = nullptr;
+  const int64_t *values = nullptr;
+  int64_t child_offset = 0;
+  bool child_may_have_nulls = false;
+
+  bool valid(int64_t i) const { return !validity || bit_set(validity, offset + i); }
+  int64_t begin(int64_t i) const {
+    return large ? static_cast<const int64_t *>(offsets)[offset + i] : static_cast<const int32_t *>(offsets)[offset + i];
+  }
+  bool child_valid(int64_t j) const { return !child_validity || bit_set(child_validity, child_offset + j); }
+};
+
+// null_count may be -1 (not computed): then the bitmap decides
+bool may_have_nulls(const ArrowArray *a) { return a->null_count != 0 && a->n_buffers > 0 && a->buffers[0] != nullptr; }
+
+int parse_key_column(cudasp_query *q, const ArrowSchema *sc, const ArrowArray *a, KeyColumn *k) {
+  if (!sc || !a || !sc->format) return stg::fail(q, CUDASP_ERR_ARG, "tweak_key: NULL schema or array");
+  const std::string f = sc->format;
+  k->offset = a->offset;
+  k->length = a->length;
+  k->may_have_nulls = may_have_nulls(a);
+  k->validity = k->may_have_nulls ? static_cast<const uint8_t *>(a->buffers[0]) : nullptr;
+  if (f.rfind("w:", 0) == 0) {
+    k->width = atoi(f.c_str() + 2);
+    if (k->width <= 0 || a->n_buffers < 2) return stg::fail(q, CUDASP_ERR_ARG, "tweak_key: malformed fixed_size_binary column");
+    k->data = static_cast<const uint8_t *>(a->buffers[1]);
+  } else if (f == "z" || f == "Z") {
+    if (a->n_buffers < 3) return stg::fail(q, CUDASP_ERR_ARG, "tweak_key: malformed binary column");
+    k->large = f == "Z";
+    k->offsets = a->buffers[1];
+    k->data = static_cast<const uint8_t *>(a->buffers[2]);
+  } else {
+    return stg::fail(q, CUDASP_ERR_ARG, "tweak_key must be fixed_size_binary(64|33), binary or large_binary");
+  }
+  if (a->length && (!k->data || (!k->width && !k->offsets))) {
+    // an all-empty binary column may legally carry a NULL data buffer; only the offsets are needed then
+    if (k->width || !k->offsets) return stg::fail(q, CUDASP_ERR_ARG, "tweak_key: missing buffer");
+  }
+  return 0;
+}
+
+int parse_list_column(cudasp_query *q, const ArrowSchema *sc, const ArrowArray *a, ListColumn *l) {
+  if (!sc || !a || !sc->format) return stg::fail(q, CUDASP_ERR_ARG, "outputs: NULL schema or array");
+  const std::string f = sc->format;
+  if (f != "+l" && f != "+L") return stg::fail(q, CUDASP_ERR_ARG, "outputs must be list<int64> or large_list<int64>");
+  if (sc->n_children != 1 || a->n_children != 1 || !sc->children[0]->format || std::string(sc->children[0]->format) != "l")
+    return stg::fail(q, CUDASP_ERR_ARG, "outputs must be a list of int64 (BIGINT)");
+  if (a->n_buffers < 2 || (a->length && !a->buffers[1])) return stg::fail(q, CUDASP_ERR_ARG, "outputs: missing offsets buffer");
+  l->large = f == "+L";
+  l->offset = a->offset;
+  l->length = a->length;
+  l->may_have_nulls = may_have_nulls(a);
+  l->validity = l->may_have_nulls ? static_cast<const uint8_t *>(a->buffers[0]) : nullptr;
+  l->offsets = a->buffers[1];
+  const ArrowArray *c = a->children[0];
+  if (c->n_buffers < 2) return stg::fail(q, CUDASP_ERR_ARG, "outputs: malformed child array");
+  l->child_offset = c->offset;
+  l->child_may_have_nulls = may_have_nulls(c);
+  l->child_validity = l->child_may_have_nulls ? static_cast<const uint8_t *>(c->buffers[0]) : nullptr;
+  l->values = static_cast<const int64_t *>(c->buffers[1]);
+  if (c->length && !l->values) return stg::fail(q, CUDASP_ERR_ARG, "outputs: missing values buffer");
+  return 0;
+}
+
+int format_of(int64_t key_size) {
+  return key_size == 64 ? CUDASP_KEYS_XY64 : key_size == 33 ? CUDASP_KEYS_SEC1_33 : -1;
+}
+
+// Streams rows of any number of (key, list) column pairs through the query's staging slots; ids come back as global
+// row numbers (row_base + index in the pair), ascending per pair, pairs in push order.
+class ArrowScanner {
+ public:
+  explicit ArrowScanner(cudasp_query *q) : q_(q), piece_(stg::piece_rows(q)) {}
+  ~ArrowScanner() {
+    for (Pending &p : pending_) {        // error exit: let the slot's stream finish before its staging is reused
+      uint32_t n = 0;
+      stg::finish(q_, &p.s, &n);
+      stg::release(q_, &p.s);
+    }
+  }
+
+  std::vector<uint64_t> matches;
+
+  int push(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity, int64_t row_validity_offset, uint64_t row_base) {
+    int64_t a = 0;
+    const int64_t n = k.length;
+    while (a < n) {
+      int rc = dense_ok(k, l, row_validity) ? stage_dense(k, l, row_base, &a) : 1;
+      if (rc < 0) return rc;
+      if (rc == 1) {
+        rc = stage_general(k, l, row_validity, row_validity_offset, row_base, &a);
+        if (rc < 0) return rc;
+      }
+    }
+    return 0;
+  }
+
+  int drain() {
+    int rc = 0;
+    while (!pending_.empty()) {
+      int r = collect_front();
+      if (!rc) rc = r;
+    }
+    return rc;
+  }
+
+ private:
+  struct Pending {
+    Staging s;
+    uint64_t base;                    // global row number of the piece's first source row
+    std::vector<uint32_t> rowmap;     // general path: staged row -> source row - base; empty = identity
+  };
+
+  cudasp_query *q_;
+  uint32_t piece_;
+  std::deque<Pending> pending_;
+
+  static bool dense_ok(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity) {
+    return !row_validity && !k.may_have_nulls && !l.may_have_nulls && !l.child_may_have_nulls;
+  }
+
+  int collect_front() {
+    Pending p = std::move(pending_.front());
+    pending_.pop_front();
+    uint32_t n = 0;
+    int rc = stg::finish(q_, &p.s, &n);
+    if (!rc) {
+      for (uint32_t i = 0; i < n; i++) {
+        const uint32_t id = p.s.ids[i];
+        matches.push_back(p.base + (p.rowmap.empty() ? id : p.rowmap[id]));
+      }
+    }
+    stg::release(q_, &p.s);
+    return rc;
+  }
+
+  int acquire(Staging *s) {
+    for (;;) {
+      int rc = stg::acquire(q_, s, false);
+      if (rc != 0) return rc < 0 ? rc : 0;
+      if (!pending_.empty()) {        // recycle our own oldest piece (keeps results in row order)
+        rc = collect_front();
+        if (rc) return rc;
+      } else {
+        rc = stg::acquire(q_, s, true);
+        return rc < 0 ? rc : 0;
+      }
+    }
+  }
+
+  // returns 0 = staged a piece (*a advanced), 1 = this piece needs the general path, < 0 = error
+  int stage_dense(const KeyColumn &k, const ListColumn &l, uint64_t row_base, int64_t *a) {
+    const int64_t base = *a;
+    const int64_t cnt = std::min<int64_t>(piece_, k.length - base);
+    const int64_t w = k.size(base);
+    const int fmt = format_of(w);
+    if (fmt < 0) return 1;
+    if (!k.width) {                   // binary column: the piece must be one uniform width
+      bool uniform = true;
+      if (k.large) {
+        const int64_t *o = static_cast<const int64_t *>(k.offsets) + k.offset + base;
+        for (int64_t i = 0; i < cnt; i++) uniform &= (o[i + 1] - o[i]) == w;
+      } else {
+        const int32_t *o = static_cast<const int32_t *>(k.offsets) + k.offset + base;
+        for (int64_t i = 0; i < cnt; i++) uniform &= (o[i + 1] - o[i]) == w;
+      }
+      if (!uniform) return 1;
+    }
+    const int64_t o0 = l.begin(base), o1 = l.begin(base + cnt);
+    const uint64_t no = (uint64_t)(o1 - o0);
+    if (o1 < o0 || no > 0xFFFFFFFFull) return stg::fail(q_, CUDASP_ERR_ARG, "outputs: offsets out of range");
+    Staging s;
+    int rc = acquire(&s);
+    if (rc) return rc;
+    if (no > s.cap_outputs && (rc = stg::reserve_outputs(q_, &s, no))) {
+      stg::release(q_, &s);
+      return rc;
+    }
+    memcpy(s.tweaks, k.data + k.begin(base), (size_t)cnt * w);
+    if (l.large) {
+      const int64_t *o = static_cast<const int64_t *>(l.offsets) + l.offset + base;
+      for (int64_t i = 0; i <= cnt; i++) s.offsets[i] = (uint32_t)(o[i] - o0);
+    } else {
+      const int32_t *o = static_cast<const int32_t *>(l.offsets) + l.offset + base;
+      for (int64_t i = 0; i <= cnt; i++) s.offsets[i] = (uint32_t)(o[i] - (int32_t)o0);
+    }
+    if (no) memcpy(s.outputs, l.values + l.child_offset + o0, no * 8);
+    rc = stg::submit(q_, &s, (uint32_t)cnt, no, fmt);
+    if (rc) {
+      stg::release(q_, &s);
+      return rc;
+    }
+    pending_.push_back(Pending{s, row_base + (uint64_t)base, {}});
+    *a = base + cnt;
+    return 0;
+  }
+
+  int stage_general(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity, int64_t rv_off, uint64_t row_base,
+                    int64_t *a);
+};
+
+// Row by row with the reference's NULL rules (src/cudasp_extension.cu:195-221).  Consumes source rows from *a until the
+// piece is full, the key format changes, or the column ends; rows that can never match are skipped.
+int ArrowScanner::stage_general(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity, int64_t rv_off,
+                                uint64_t row_base, int64_t *a) {
+  const int64_t n = k.length;
+  int64_t i = *a;
+  // skip leading rows that are dropped anyway, so that an all-NULL stretch does not cost a slot
+  auto dropped = [&](int64_t r) {
+    return (row_validity && !bit_set(row_validity, rv_off + r)) || !k.valid(r) || format_of(k.size(r)) < 0;
+  };
+  while (i < n && dropped(i)) i++;
+  if (i == n) {
+    *a = n;
+    return 0;
+  }
+  const int64_t first = i;
+  const int64_t w = k.size(first);
+  const int fmt = format_of(w);
+  Staging s;
+  int rc = acquire(&s);
+  if (rc) return rc;
+  Pending p{s, row_base + (uint64_t)first, {}};
+  const uint32_t cap = std::min<uint32_t>(piece_, p.s.cap_rows);
+  p.rowmap.reserve(cap);
+  uint32_t rows = 0;
+  uint64_t n_out = 0;
+  p.s.offsets[0] = 0;
+  for (; i < n && rows < cap; i++) {
+    if (dropped(i)) continue;
+    if (k.size(i) != w) break;                       // the other key format: next piece
+    int64_t b = 0, e = 0;
+    if (l.valid(i)) {
+      b = l.begin(i);
+      e = l.begin(i + 1);
+      if (e < b) {
+        stg::release(q_, &p.s);
+        return stg::fail(q_, CUDASP_ERR_ARG, "outputs: offsets not monotonic");
+      }
+    }
+    const uint64_t len = (uint64_t)(e - b);
+    if (n_out + len > p.s.cap_outputs) {
+      if (rows) break;                               // cut the piece here
+      if ((rc = stg::reserve_outputs(q_, &p.s, len))) {
+        stg::release(q_, &p.s);
+        return rc;
+      }
+    }
+    memcpy(p.s.tweaks + (size_t)rows * w, k.data + k.begin(i), (size_t)w);
+    if (l.child_validity) {
+      for (int64_t j = b; j < e; j++)
+        if (l.child_valid(j)) p.s.outputs[n_out++] = l.values[l.child_offset + j];
+    } else if (len) {
+      memcpy(p.s.outputs + n_out, l.values + l.child_offset + b, len * 8);
+      n_out += len;
+    }
+    if (n_out > 0xFFFFFFFFull) {
+      stg::release(q_, &p.s);
+      return stg::fail(q_, CUDASP_ERR_ARG, "outputs: more than 2^32 values in one piece");
+    }
+    p.rowmap.push_back((uint32_t)(i - first));
+    p.s.offsets[++rows] = (uint32_t)n_out;
+  }
+  *a = i;
+  rc = stg::submit(q_, &p.s, rows, n_out, fmt);
+  if (rc) {
+    stg::release(q_, &p.s);
+    return rc;
+  }
+  pending_.push_back(std::move(p));
+  return 0;
+}
+
+int copy_out(cudasp_query *q, const std::vector<uint64_t> &m, uint64_t *match_rows, uint64_t capacity, uint64_t *n_matches) {
+  *n_matches = m.size();
+  if (m.size() > capacity) return stg::fail(q, CUDASP_ERR_ARG, "match_rows capacity too small");
+  if (!m.empty()) memcpy(match_rows, m.data(), m.size() * sizeof(uint64_t));
+  return CUDASP_OK;
+}
+
+struct BatchColumns {
+  KeyColumn key;
+  ListColumn list;
+  const uint8_t *row_validity = nullptr;
+  int64_t row_validity_offset = 0;
+};
+
+// children of a struct array are NOT sliced by the parent's offset: logical row i = child row (parent.offset + i)
+int parse_batch(cudasp_query *q, const ArrowSchema *schema, const ArrowArray *batch, int tweak_col, int outputs_col, BatchColumns *bc) {
+  if (!schema || !batch || !schema->format) return stg::fail(q, CUDASP_ERR_ARG, "NULL schema or batch");
+  if (std::string(schema->format) != "+s") return stg::fail(q, CUDASP_ERR_ARG, "a record batch must be a struct array (+s)");
+  if (tweak_col < 0 || outputs_col < 0 || tweak_col >= schema->n_children || outputs_col >= schema->n_children ||
+      schema->n_children != batch->n_children)
+    return stg::fail(q, CUDASP_ERR_ARG, "column index out of range");
+  int rc = parse_key_column(q, schema->children[tweak_col], batch->children[tweak_col], &bc->key);
+  if (rc) return rc;
+  rc = parse_list_column(q, schema->children[outputs_col], batch->children[outputs_col], &bc->list);
+  if (rc) return rc;
+  bc->key.offset += batch->offset;
+  bc->list.offset += batch->offset;
+  if (bc->key.length < batch->length || bc->list.length < batch->length)
+    return stg::fail(q, CUDASP_ERR_ARG, "a column is shorter than the batch");
+  bc->key.length = bc->list.length = batch->length;
+  if (may_have_nulls(batch)) {
+    bc->row_validity = static_cast<const uint8_t *>(batch->buffers[0]);
+    bc->row_validity_offset = batch->offset;
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cudasp_scan_arrow_columns(cudasp_query *q, const ArrowSchema *tweak_schema, const ArrowArray *tweak_key,
+                              const ArrowSchema *outputs_schema, const ArrowArray *outputs, uint64_t *match_rows,
+                              uint64_t capacity, uint64_t *n_matches) {
+  if (!q || !n_matches || (capacity && !match_rows)) return stg::fail(q, CUDASP_ERR_ARG, "NULL argument");
+  *n_matches = 0;
+  KeyColumn k;
+  ListColumn l;
+  int rc = parse_key_column(q, tweak_schema, tweak_key, &k);
+  if (rc) return rc;
+  if ((rc = parse_list_column(q, outputs_schema, outputs, &l))) return rc;
+  if (k.length != l.length) return stg::fail(q, CUDASP_ERR_ARG, "tweak_key and outputs differ in length");
+  ArrowScanner sc(q);
+  if ((rc = sc.push(k, l, nullptr, 0, 0))) return rc;
+  if ((rc = sc.drain())) return rc;
+  return copy_out(q, sc.matches, match_rows, capacity, n_matches);
+}
+
+int cudasp_scan_arrow(cudasp_query *q, const ArrowSchema *schema, const ArrowArray *batch, int tweak_col, int outputs_col,
+                      uint64_t *match_rows, uint64_t capacity, uint64_t *n_matches) {
+  if (!q || !n_matches || (capacity && !match_rows)) return stg::fail(q, CUDASP_ERR_ARG, "NULL argument");
+  *n_matches = 0;
+  BatchColumns bc;
+  int rc = parse_batch(q, schema, batch, tweak_col, outputs_col, &bc);
+  if (rc) return rc;
+  ArrowScanner sc(q);
+  if ((rc = sc.push(bc.key, bc.list, bc.row_validity, bc.row_validity_offset, 0))) return rc;
+  if ((rc = sc.drain())) return rc;
+  return copy_out(q, sc.matches, match_rows, capacity, n_matches);
+}
+
+int cudasp_scan_arrow_stream(cudasp_query *q, ArrowArrayStream *stream, int tweak_col, int outputs_col, uint64_t **match_rows,
+                             uint64_t *n_matches, uint64_t *rows_seen) {
+  if (!q || !stream || !match_rows || !n_matches) return stg::fail(q, CUDASP_ERR_ARG, "NULL argument");
+  *match_rows = nullptr;
+  *n_matches = 0;
+  if (rows_seen) *rows_seen = 0;
+  ArrowSchema schema;
+  memset(&schema, 0, sizeof schema);
+  if (stream->get_schema(stream, &schema) != 0) {
+    const char *e = stream->get_last_error ? stream->get_last_error(stream) : nullptr;
+    return stg::fail(q, CUDASP_ERR_ARG, e ? e : "ArrowArrayStream.get_schema failed");
+  }
+  ArrowScanner sc(q);
+  uint64_t base = 0;
+  int rc = 0;
+  for (;;) {
+    ArrowArray batch;
+    memset(&batch, 0, sizeof batch);
+    if (stream->get_next(stream, &batch) != 0) {
+      const char *e = stream->get_last_error ? stream->get_last_error(stream) : nullptr;
+      rc = stg::fail(q, CUDASP_ERR_ARG, e ? e : "ArrowArrayStream.get_next failed");
+      break;
+    }
+    if (!batch.release) break;          // end of stream
+    BatchColumns bc;
+    rc = parse_batch(q, &schema, &batch, tweak_col, outputs_col, &bc);
+    if (!rc) rc = sc.push(bc.key, bc.list, bc.row_validity, bc.row_validity_offset, base);
+    base += (uint64_t)batch.length;
+    batch.release(&batch);              // staged into pinned memory: the batch is no longer needed
+    if (rc) break;
+  }
+  if (schema.release) schema.release(&schema);
+  int r2 = sc.drain();
+  if (!rc) rc = r2;
+  if (rc) return rc;
+  if (rows_seen) *rows_seen = base;
+  *n_matches = sc.matches.size();
+  if (!sc.matches.empty()) {
+    *match_rows = static_cast<uint64_t *>(malloc(sc.matches.size() * sizeof(uint64_t)));
+    if (!*match_rows) return stg::fail(q, CUDASP_ERR_STATE, "out of memory");
+    memcpy(*match_rows, sc.matches.data(), sc.matches.size() * sizeof(uint64_t));
+  }
+  return CUDASP_OK;
+}
+
+void cudasp_free(void *p) { free(p); }
+
+}  // extern "C"

@@ -22,6 +22,7 @@
 #include "../../include/cudasp.h"
 #include "kernels.cuh"
 #include "query_plan.hpp"
+#include "staging_internal.hpp"
 
 using namespace csp;
 
@@ -633,6 +634,48 @@ int finish(cudasp_query *q, Slot *s, uint32_t *n_matches) {
 }
 
 }  // namespace
+
+// ---- internal staging interface for host-only ingest front-ends (staging_internal.hpp) --------
+namespace csp {
+namespace staging {
+static void view(Staging *v, Slot *s) {
+  v->slot = s;
+  v->tweaks = s->h_tweaks;
+  v->outputs = s->h_outputs;
+  v->offsets = s->h_off;
+  v->ids = s->h_result + 1;
+  v->cap_rows = s->cap_rows;
+  v->cap_outputs = s->cap_outputs;
+}
+int acquire(cudasp_query *q, Staging *v, bool block) {
+  int rc = 0;
+  Slot *s = block ? acquire_blocking(q, &rc) : try_acquire(q, &rc);
+  if (!s) return rc;
+  s->internal = true;
+  view(v, s);
+  return 1;
+}
+int reserve_outputs(cudasp_query *q, Staging *v, uint64_t n) {
+  Slot *s = static_cast<Slot *>(v->slot);
+  if (n <= s->cap_outputs) return 0;
+  cudaSetDevice(q->devs[s->dev_index].device);
+  cudaStreamSynchronize(s->stream);
+  int rc = alloc_slot_outputs(q, *s, n + n / 4);
+  view(v, s);
+  return rc;
+}
+int submit(cudasp_query *q, Staging *v, uint32_t rows, uint64_t n_outputs, int key_format) {
+  return ::submit(q, static_cast<Slot *>(v->slot), rows, n_outputs, 0, key_format);
+}
+int finish(cudasp_query *q, Staging *v, uint32_t *n) { return ::finish(q, static_cast<Slot *>(v->slot), n); }
+void release(cudasp_query *q, Staging *v) {
+  if (v->slot) release_slot(q, static_cast<Slot *>(v->slot));
+  v->slot = nullptr;
+}
+uint32_t piece_rows(cudasp_query *q) { return std::min<uint32_t>(q->batch_rows, q->piece_rows); }
+int fail(cudasp_query *q, int code, const char *msg) { return ::fail(q, code, msg); }
+}  // namespace staging
+}  // namespace csp
 
 // =====================================================================================
 extern "C" {

@@ -28,6 +28,19 @@ def test_exports_match_header(M):
     assert b"sm_100a" in L.cudasp_version()
 
 
+def test_arrow_exports_match_header(M):
+    hdr = open(os.path.join(ROOT, "include", "cudasp_arrow.h")).read()
+    declared = set(re.findall(r"\b(cudasp_[a-z_]+)\s*\(", hdr))
+    assert declared == set(M.ARROW_EXPORTS), declared ^ set(M.ARROW_EXPORTS)
+    L = M.lib()
+    for name in declared:
+        assert getattr(L, name) is not None
+    # the internal staging interface between the two translation units stays internal
+    import subprocess
+    syms = subprocess.run(["nm", "-D", "--defined-only", M.LIB_PATH], capture_output=True, text=True).stdout
+    assert "staging" not in syms
+
+
 def test_no_cpu_fallback(M):
     import torch
     if torch.cuda.is_available():
