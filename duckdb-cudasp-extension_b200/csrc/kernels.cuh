@@ -70,7 +70,8 @@ template <int BLOCK, int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) k_hash_fixedbase(fe *__restrict__ X, fe *__restrict__ Y, fe *__restrict__ Z,
                                                                 uint32_t rows, const ge *__restrict__ gtab,
                                                                 const __grid_constant__ FinalParams fp,
-                                                                uint8_t *__restrict__ dbg_S, uint8_t *__restrict__ dbg_t) {
+                                                                uint8_t *__restrict__ dbg_S, uint8_t *__restrict__ dbg_t,
+                                                                fe *__restrict__ keep_sx, uint8_t *__restrict__ keep_sodd) {
   const uint32_t row = blockIdx.x * BLOCK + threadIdx.x;
   if (row >= rows) return;
   fe x, y, zi, sx, sy, t;
@@ -78,8 +79,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_hash_fixedbase(fe *__restrict__
   load_fe(y, Y + row);
   load_fe(zi, Z + row);   // already inverted by k_batch_inv
   gej acc;
-  const bool dbg = dbg_S || dbg_t;
+  const bool dbg = dbg_S || dbg_t || keep_sx;
   hash_fixedbase_row(acc, x, y, zi, gtab, fp, dbg ? &sx : nullptr, dbg ? &sy : nullptr, dbg ? &t : nullptr);
+  if (keep_sx) {          // match details enabled: the compressed shared secret outlives this kernel (33 B/row)
+    store_fe(keep_sx + row, sx);
+    keep_sodd[row] = (uint8_t)(sy.v[0] & 1u);
+  }
   if (dbg_S) {
     uint32_t *o = reinterpret_cast<uint32_t *>(dbg_S + (size_t)row * 64);
 #pragma unroll
@@ -209,6 +214,38 @@ __global__ void k_test_field(int op, const fe *__restrict__ a, const fe *__restr
   }
   fe_normalize(r);
   store_fe(out + i, r);
+}
+
+// ---------------------------------------------------------------- K8 (opt-in): match details
+// One thread per MATCHED row (a handful per batch): the BIP-352 k-loop of details_row.  The grid is fixed and strides
+// over the device-side match count, so no host round trip is needed to size it.  One warp per block spreads the few
+// rows over the SMs; each record is appended with one atomic.
+__global__ void __launch_bounds__(32) k_details(const fe *__restrict__ SX, const uint8_t *__restrict__ SODD,
+                                                const uint32_t *__restrict__ match_ids, const uint32_t *__restrict__ n_matches,
+                                                const int64_t *__restrict__ outputs, const uint32_t *__restrict__ out_off,
+                                                const ge *__restrict__ labels, uint32_t n_labels, const ge *__restrict__ gtab,
+                                                const __grid_constant__ FinalParams fp, MatchDetail *__restrict__ out,
+                                                uint32_t *__restrict__ n_out, uint32_t cap) {
+  const uint32_t n = *n_matches;
+  for (uint32_t m = blockIdx.x * 32 + threadIdx.x; m < n; m += gridDim.x * 32) {
+    const uint32_t row = match_ids[m];
+    fe sx;
+    load_fe(sx, SX + row);
+    details_row(sx, SODD[row], outputs, out_off[row], out_off[row + 1], labels, n_labels, gtab, fp,
+                [&](uint32_t k, uint32_t oi, int32_t li, const fe &t) {
+                  const uint32_t at = atomicAdd(n_out, 1u);
+                  if (at >= cap) return;          // counted, not stored: the host reports the overflow
+                  MatchDetail d;
+                  d.row = row; d.k = k; d.output_index = oi; d.label_index = li;
+#pragma unroll
+                  for (int l = 0; l < 8; l++) {
+                    const uint32_t wv = t.v[7 - l];
+                    d.t_k[4 * l] = (uint8_t)(wv >> 24); d.t_k[4 * l + 1] = (uint8_t)(wv >> 16);
+                    d.t_k[4 * l + 2] = (uint8_t)(wv >> 8); d.t_k[4 * l + 3] = (uint8_t)wv;
+                  }
+                  out[at] = d;
+                });
+  }
 }
 
 }  // namespace csp

@@ -226,32 +226,8 @@ CSP_HD void batch_inv_thread(fe *vals, fe *scratch, uint32_t n, uint32_t T, uint
   }
 }
 
-// ---------------------------------------------------------------- K3 body: hash, t*G, + B_spend
-// in : shared secret S as Jacobian (X, Y) plus Zinv from the batch inversion
-// out: P0 = t*G + B_spend as Jacobian.
-// t*G uses the offset fixed-window table gtab[w][d] = (d * 2^(13w) + r_w) * G (affine, 64 B per
-// entry, 20 x 8192 entries = 10 MB, L2-resident): 19 mixed additions, no zero digits, no doublings.  The
-// constant (sum r_w)*G is removed by adding spend_adj = B_spend - (sum r_w)*G instead of B_spend.
-// sx, sy, t_out (optional) receive the affine shared secret and the hash for the intermediates API.
-CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zinv, const ge *gtab, const FinalParams &fp,
-                               fe *sx, fe *sy, fe *t_out) {
-  fe x, y;
-  if (fp.zero_scalar) {
-    fe_set_zero(x); fe_set_zero(y);
-  } else {
-    fe zi2, zi3;
-    fe_sqr(zi2, Zinv);
-    fe_mul(zi3, zi2, Zinv);
-    fe_mul(x, X, zi2);
-    fe_mul(y, Y, zi3);
-    fe_normalize(x);
-    fe_normalize(y);
-  }
-  if (sx) *sx = x;
-  if (sy) *sy = y;
-  fe t;
-  bip352_shared_secret_hash(t, x, y.v[0] & 1u, fp.midstate);
-  if (t_out) *t_out = t;
+// acc = t*G + B_spend from the offset window table (see the comment below); t is taken as a 256-bit integer, not reduced.
+CSP_HD void fixedbase_plus_spend(gej &acc, const fe &t, const ge *gtab, const FinalParams &fp) {
   // all digits first (static limb indices: t stays in registers), then a one-entry-ahead prefetch pipeline
   uint32_t dg[GTAB_NWIN];
 #if defined(__CUDA_ARCH__)
@@ -286,6 +262,35 @@ CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zin
     qx = nx; qy = ny;
   }
   if (!fp.spend_adj_inf) gej_add_ge(acc, acc, fp.spend_adj_x, fp.spend_adj_y);
+}
+
+// ---------------------------------------------------------------- K3 body: hash, t*G, + B_spend
+// in : shared secret S as Jacobian (X, Y) plus Zinv from the batch inversion
+// out: P0 = t*G + B_spend as Jacobian.
+// t*G uses the offset fixed-window table gtab[w][d] = (d * 2^(13w) + r_w) * G (affine, 64 B per
+// entry, 20 x 8192 entries = 10 MB, L2-resident): 19 mixed additions, no zero digits, no doublings.  The
+// constant (sum r_w)*G is removed by adding spend_adj = B_spend - (sum r_w)*G instead of B_spend.
+// sx, sy, t_out (optional) receive the affine shared secret and the hash for the intermediates API.
+CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zinv, const ge *gtab, const FinalParams &fp,
+                               fe *sx, fe *sy, fe *t_out) {
+  fe x, y;
+  if (fp.zero_scalar) {
+    fe_set_zero(x); fe_set_zero(y);
+  } else {
+    fe zi2, zi3;
+    fe_sqr(zi2, Zinv);
+    fe_mul(zi3, zi2, Zinv);
+    fe_mul(x, X, zi2);
+    fe_mul(y, Y, zi3);
+    fe_normalize(x);
+    fe_normalize(y);
+  }
+  if (sx) *sx = x;
+  if (sy) *sy = y;
+  fe t;
+  bip352_shared_secret_hash(t, x, y.v[0] & 1u, fp.midstate);
+  if (t_out) *t_out = t;
+  fixedbase_plus_spend(acc, t, gtab, fp);
 }
 
 // ---------------------------------------------------------------- K5/K7 bodies
@@ -333,6 +338,76 @@ CSP_HD int64_t label_candidate(const fe &x0, const fe &y0, const fe &lx, const f
   fe_lin3<1, -1, -1>(x, x, x0, lx);
   fe_normalize(x);
   return upper64(x);
+}
+
+// ---------------------------------------------------------------- match details (opt-in, SURVEY 8f rank 3+4)
+// Full BIP-352 receive loop for ONE row that already matched at k = 0 (BIP-352 "Scanning", with the reference's data
+// model: outputs are 64-bit x prefixes, the label set is the query's label_keys):
+//   k = 0;  loop:  t_k = hash(ser(S) || ser32(k));  stop if t_k == 0 or t_k >= n
+//                  P_k = B_spend + t_k*G;  candidates c_0 = pre(x(P_k)), c_i = pre(x(P_k + L_i))
+//                  first remaining output (list order) equal to c_0, else to the first matching c_i, is recorded
+//                  as (row, k, output index, label or -1, t_k), removed from the set, k++;  none found -> stop
+// The default path (k = 0 only, t not range-checked, src/cudasp_gpu.cu:278-282,869-876) is untouched by this pass:
+// it only ADDS information about rows the default path reports.
+struct MatchDetail {           // == cudasp_match_detail (include/cudasp.h)
+  uint32_t row, k, output_index;
+  int32_t label_index;
+  uint8_t t_k[32];
+};
+static const uint32_t DETAILS_MAX_K = 32;      // more outputs to one recipient in one transaction than this are not followed
+
+CSP_HD bool tweak_in_range(const fe &t) {      // 0 < t < n  (n = group order)
+  const uint32_t n[8] = {0xD0364141u, 0xBFD25E8Cu, 0xAF48A03Bu, 0xBAAEDCE6u, 0xFFFFFFFEu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+  uint32_t any = 0;
+  bool lt = false;
+  for (int i = 7; i >= 0; i--) {
+    any |= t.v[i];
+    if (t.v[i] != n[i]) { lt = t.v[i] < n[i]; break; }
+  }
+  for (int i = 0; i < 8; i++) any |= t.v[i];
+  return any != 0 && lt;
+}
+
+// emit(k, output_index, label_index, t) is called once per recorded output; returns the number recorded.
+template <class Emit>
+CSP_HD uint32_t details_row(const fe &sx, uint32_t s_odd, const int64_t *outputs, uint32_t lo, uint32_t hi, const ge *labels,
+                            uint32_t n_labels, const ge *gtab, const FinalParams &fp, Emit emit) {
+  uint32_t used[DETAILS_MAX_K];
+  uint32_t found = 0;
+  for (uint32_t k = 0; k < DETAILS_MAX_K && lo + found < hi; k++) {
+    fe t;
+    bip352_shared_secret_hash_k(t, sx, s_odd, k, fp.midstate);
+    if (!tweak_in_range(t)) break;
+    gej acc;
+    fixedbase_plus_spend(acc, t, gtab, fp);
+    fe zi, x0, y0;
+    fe_inv(zi, acc.z);
+    const int64_t c0 = base_candidate(x0, &y0, acc.x, acc.y, zi);
+    int32_t hit_label = -2;
+    uint32_t hit_out = 0;
+    // outputs in list order; for each, P_k itself first, then the labels in order (BIP-352 "Scanning")
+    for (uint32_t j = lo; j < hi && hit_label == -2; j++) {
+      bool gone = false;
+      for (uint32_t u = 0; u < found; u++) gone |= used[u] == j;
+      if (gone) continue;
+      const int64_t o = outputs[j];
+      if (o == c0) { hit_label = -1; hit_out = j; break; }
+      for (uint32_t i = 0; i < n_labels; i++) {
+        fe lx, ly, d;
+        load_fe_ro(lx, &labels[i].x);
+        load_fe_ro(ly, &labels[i].y);
+        fe_sub(d, lx, x0);                     // same candidate rule as K5/K7 (label_candidate), private inversion
+        fe_normalize(d);
+        if (!fe_is_zero(d)) fe_inv(d, d);
+        const int64_t c = label_candidate(x0, y0, lx, ly, d);
+        if (o == c) { hit_label = (int32_t)i; hit_out = j; break; }
+      }
+    }
+    if (hit_label == -2) break;
+    used[found++] = hit_out;
+    emit(k, hit_out - lo, hit_label, t);
+  }
+  return found;
 }
 
 }  // namespace csp

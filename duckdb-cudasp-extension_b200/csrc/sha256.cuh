@@ -66,13 +66,15 @@ CSP_HD void sha256_compress(uint32_t st[8], uint32_t w[16]) {
 // (t.v[7] most significant).  x must be canonical; y_odd is the parity of the canonical y.
 // midstate = chaining value after the TH||TH block.  k = 0 is hard-wired like the reference
 // (src/cudasp_gpu.cu:278-282); the value is NOT reduced mod n (src/cudasp_gpu.cu:869-876).
-CSP_HD void bip352_shared_secret_hash(fe &t, const fe &x, uint32_t y_odd, const uint32_t midstate[8]) {
+// bip352_shared_secret_hash_k: the same with the output counter k of BIP-352 (ser_32(k), big-endian) -- only the
+// opt-in match-details pass iterates k > 0.
+CSP_HD void bip352_shared_secret_hash_k(fe &t, const fe &x, uint32_t y_odd, uint32_t k, const uint32_t midstate[8]) {
   uint32_t w[16];
   w[0] = ((0x02u + (y_odd & 1u)) << 24) | (x.v[7] >> 8);
 #pragma unroll
   for (int j = 1; j < 8; j++) w[j] = (x.v[8 - j] << 24) | (x.v[7 - j] >> 8);
-  w[8] = x.v[0] << 24;      // last x byte, then the three leading zero bytes of k
-  w[9] = 0x00800000u;       // fourth zero byte of k, then the 0x80 pad
+  w[8] = (x.v[0] << 24) | (k >> 8);        // last x byte, then the three leading bytes of k
+  w[9] = (k << 24) | 0x00800000u;          // fourth byte of k, then the 0x80 pad
   w[10] = w[11] = w[12] = w[13] = w[14] = 0;
   w[15] = (64 + 37) * 8;    // 808 bits
   uint32_t st[8];
@@ -81,6 +83,9 @@ CSP_HD void bip352_shared_secret_hash(fe &t, const fe &x, uint32_t y_odd, const 
   sha256_compress(st, w);
 #pragma unroll
   for (int i = 0; i < 8; i++) t.v[i] = st[7 - i];
+}
+CSP_HD void bip352_shared_secret_hash(fe &t, const fe &x, uint32_t y_odd, const uint32_t midstate[8]) {
+  bip352_shared_secret_hash_k(t, x, y_odd, 0u, midstate);
 }
 
 }  // namespace csp
