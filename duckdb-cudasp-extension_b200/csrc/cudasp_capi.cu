@@ -12,6 +12,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <atomic>
 #include <condition_variable>
 #include <deque>
@@ -24,6 +25,8 @@
 #include "query_plan.hpp"
 #include "staging_internal.hpp"
 
+static_assert(sizeof(csp::MatchDetail) == sizeof(cudasp_match_detail) && sizeof(cudasp_match_detail) == 48, "detail record layout");
+
 using namespace csp;
 
 namespace {
@@ -32,6 +35,8 @@ thread_local std::string tl_err;
 
 const int SLOTS_PER_DEVICE = 6, MAX_SLOTS_PER_DEVICE = 64;   // 6: measured, a 3-deep queue lets the GPU run dry (profiles/r01e)
 const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
+const uint32_t EAGER_DETAILS = 32; // detail records copied back together with their count
+const uint32_t DETAILS_GRID = 64;  // K8: 64 one-warp blocks stride over the matched rows
 const uint32_t SYNC_PIECE_WAVES = 2;       // cudasp_scan_batch streams a large call in pieces of this many K1 waves
 const int LADDER_BLOCK = 128, LADDER_MINB = 3;
 const int HASH_BLOCK = 128, HASH_MINB = 3;
@@ -67,6 +72,12 @@ struct Slot {
   uint32_t cap_rows = 0;
   uint64_t cap_outputs = 0;
   Workspace ws;
+  // match details (opt-in, cudasp_query_enable_details): entry 0 of each buffer is a header whose first word is the count
+  MatchDetail *d_det = nullptr, *h_det = nullptr;
+  fe *keep_sx = nullptr;          // cap_rows: affine x of the shared secret, kept by K3 for K8
+  uint8_t *keep_sodd = nullptr;   // cap_rows: parity of its y
+  uint32_t det_cap = 0;
+  uint32_t n_det = 0;             // after finish()
   // state
   int state = 0;                  // 0 free, 1 acquired, 2 in flight, 3 result handed out
   uint64_t tag = 0;
@@ -92,6 +103,7 @@ struct cudasp_query {
   uint32_t n_labels = 0;
   uint32_t batch_rows = 0;
   uint64_t max_outputs = 0;
+  uint32_t details_cap = 0;      // > 0: match details enabled, records per batch
   uint32_t piece_rows = 0;       // rows per piece of the synchronous call: whole K1 waves (SMs x 4 blocks x 128 rows)
   std::vector<DevCtx> devs;
   std::vector<Slot *> all_slots;
@@ -191,6 +203,7 @@ int alloc_slot(cudasp_query *q, Slot &s, int device, uint32_t rows, uint64_t cap
 void free_slot(Slot &s) {
   cudaFreeHost(s.h_tweaks); cudaFreeHost(s.h_outputs); cudaFreeHost(s.h_off); cudaFreeHost(s.h_result);
   cudaFree(s.d_tweaks); cudaFree(s.d_outputs); cudaFree(s.d_off); cudaFree(s.d_result);
+  cudaFreeHost(s.h_det); cudaFree(s.d_det); cudaFree(s.keep_sx); cudaFree(s.keep_sodd);
   free_workspace(s.ws);
   if (s.done) cudaEventDestroy(s.done);
   for (int i = 0; i < 3; i++) if (s.tr[i]) cudaEventDestroy(s.tr[i]);
@@ -299,16 +312,39 @@ void launch_ladder(int variant, int keyfmt, const uint8_t *d_tweaks, fe *X, fe *
   }
 }
 
+struct DetailSink {          // where K3 keeps the shared secrets and K8 appends its records
+  fe *keep_sx;
+  uint8_t *keep_sodd;
+  MatchDetail *out;          // out[0] is the header (count in its first word), records start at out[1]
+  uint32_t cap;
+};
+// (re)allocate the slot's detail buffers for the query's capacity; slots come from the cache or are materialised lazily,
+// so this is checked on every submit (a compare when nothing is to do)
+int ensure_details(cudasp_query *q, Slot &s) {
+  if (s.det_cap >= q->details_cap && s.keep_sx) return 0;
+  CU(q, cudaStreamSynchronize(s.stream));
+  cudaFreeHost(s.h_det); cudaFree(s.d_det); cudaFree(s.keep_sx); cudaFree(s.keep_sodd);
+  s.h_det = s.d_det = nullptr; s.keep_sx = nullptr; s.keep_sodd = nullptr; s.det_cap = 0;
+  const size_t n = (size_t)q->details_cap + 1;
+  CU(q, cudaHostAlloc((void **)&s.h_det, n * sizeof(MatchDetail), cudaHostAllocDefault));
+  CU(q, cudaMalloc(&s.d_det, n * sizeof(MatchDetail)));
+  CU(q, cudaMalloc(&s.keep_sx, (size_t)s.cap_rows * sizeof(fe)));
+  CU(q, cudaMalloc(&s.keep_sodd, s.cap_rows));
+  s.det_cap = q->details_cap;
+  return 0;
+}
+
 // Enqueue the whole per-batch pipeline on `st`.  All pointers are device pointers.
 // d_result: [0] = match count (reset here), [1..] = ids.  Either may be NULL (candidate mode).
 int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_tweaks, const int64_t *d_outputs,
                     const uint32_t *d_off, uint32_t rows, uint32_t *d_ids, uint32_t *d_count, cudaStream_t st,
                     int64_t *d_cands, uint8_t *dbg_S, uint8_t *dbg_t, uint8_t *dbg_P0, cudaEvent_t *stage_evs = nullptr,
-                    int keyfmt = CUDASP_KEYS_XY64) {
+                    int keyfmt = CUDASP_KEYS_XY64, const DetailSink *det = nullptr) {
   // stage_evs (profiling entry only): 8 events recorded before each of the 7 possible kernels and
   // after the last one; a stage that does not run records its event anyway (zero duration).
   int ev_i = 0;
   auto mark = [&]() { if (stage_evs) cudaEventRecord(stage_evs[ev_i++], st); };
+  if (det) CU(q, cudaMemsetAsync(det->out, 0, 4, st));
   if (rows == 0) {
     if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
     return 0;
@@ -337,7 +373,8 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
   mark();
   {
     const uint32_t grid = (rows + HASH_BLOCK - 1) / HASH_BLOCK;
-    k_hash_fixedbase<HASH_BLOCK, HASH_MINB><<<grid, HASH_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, dc.d_gtab, pl.fp, dbg_S, dbg_t);
+    k_hash_fixedbase<HASH_BLOCK, HASH_MINB><<<grid, HASH_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, dc.d_gtab, pl.fp, dbg_S, dbg_t,
+                                                                         det ? det->keep_sx : nullptr, det ? det->keep_sodd : nullptr);
     mark();
     const uint32_t T = inv_threads(rows);
     k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
@@ -360,6 +397,11 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
       mark();
     }
     mark();
+  }
+  if (det && d_ids && d_count && d_outputs) {      // K8: the BIP-352 k-loop over the rows that matched (a handful)
+    k_details<<<DETAILS_GRID, 32, 0, st>>>(det->keep_sx, det->keep_sodd, d_ids, d_count, d_outputs, d_off, dc.d_labels, L, dc.d_gtab,
+                                          pl.fp, det->out + 1, reinterpret_cast<uint32_t *>(det->out), det->cap);
+    nl += 1;
   }
   CU(q, cudaGetLastError());
   q->launches += nl;
@@ -598,9 +640,20 @@ int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t
   }
   if (trace) cudaEventRecord(s->tr[1], st);
   CU(q, cudaStreamWaitEvent(st, s->ws.free_evt, 0));
+  DetailSink sink{};
+  const bool details = q->details_cap != 0;
+  s->n_det = 0;
+  if (details) {
+    int r = ensure_details(q, *s);
+    if (r) return r;
+    sink = DetailSink{s->keep_sx, s->keep_sodd, s->d_det, q->details_cap};   // a cached slot may hold more
+  }
   int rc = launch_pipeline(q, dc, s->ws, s->d_tweaks, s->d_outputs, s->d_off, rows, s->d_result + 1, s->d_result, st,
-                           nullptr, nullptr, nullptr, nullptr, nullptr, keyfmt);
+                           nullptr, nullptr, nullptr, nullptr, nullptr, keyfmt, details ? &sink : nullptr);
   if (rc) return rc;
+  if (details)
+    CU(q, cudaMemcpyAsync(s->h_det, s->d_det, ((size_t)std::min(q->details_cap, EAGER_DETAILS) + 1) * sizeof(MatchDetail),
+                          cudaMemcpyDeviceToHost, st));
   if (trace) cudaEventRecord(s->tr[2], st);
   CU(q, cudaEventRecord(s->ws.free_evt, st));
   const uint32_t eager = std::min<uint32_t>(rows, EAGER_IDS);
@@ -630,6 +683,19 @@ int finish(cudasp_query *q, Slot *s, uint32_t *n_matches) {
   }
   std::sort(s->h_result + 1, s->h_result + 1 + n);
   *n_matches = n;
+  if (q->details_cap && s->h_det && s->rows) {
+    const uint32_t nd = *reinterpret_cast<const uint32_t *>(s->h_det);
+    if (nd > q->details_cap) return fail(q, CUDASP_ERR_STATE, "more match details than max_details_per_batch: raise it");
+    if (nd > EAGER_DETAILS) {
+      CU(q, cudaMemcpyAsync(s->h_det + 1 + EAGER_DETAILS, s->d_det + 1 + EAGER_DETAILS, ((size_t)nd - EAGER_DETAILS) * sizeof(MatchDetail),
+                            cudaMemcpyDeviceToHost, s->stream));
+      CU(q, cudaStreamSynchronize(s->stream));
+    }
+    std::sort(s->h_det + 1, s->h_det + 1 + nd, [](const MatchDetail &a, const MatchDetail &b) {
+      return a.row != b.row ? a.row < b.row : a.k < b.k;
+    });
+    s->n_det = nd;
+  }
   return 0;
 }
 
@@ -776,8 +842,48 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
   return cudasp_scan_batch_fmt(q, tweak_keys, CUDASP_KEYS_XY64, outputs, out_offsets, rows, match_ids, n_matches);
 }
 
+static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                           const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches,
+                           cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details);
+
 int cudasp_scan_batch_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
                           const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches) {
+  return scan_batch_impl(q, tweak_keys, key_format, outputs, out_offsets, rows, match_ids, n_matches, nullptr, 0, nullptr);
+}
+
+int cudasp_scan_batch_details(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                              const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches,
+                              cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details) {
+  if (!q || !n_details || (details_capacity && !details)) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  if (!q->details_cap) return fail(q, CUDASP_ERR_STATE, "match details are not enabled: call cudasp_query_enable_details first");
+  return scan_batch_impl(q, tweak_keys, key_format, outputs, out_offsets, rows, match_ids, n_matches, details, details_capacity,
+                         n_details);
+}
+
+int cudasp_query_enable_details(cudasp_query *q, uint32_t max_details_per_batch) {
+  if (!q) return fail(q, CUDASP_ERR_ARG, "NULL query");
+  std::lock_guard<std::mutex> lk(q->mu);
+  for (Slot *s : q->all_slots)
+    if (s->state != 0) return fail(q, CUDASP_ERR_STATE, "enable details before the first batch is acquired");
+  q->details_cap = max_details_per_batch ? max_details_per_batch : std::min<uint32_t>(q->batch_rows, 65536u);
+  return CUDASP_OK;
+}
+
+int cudasp_result_details(cudasp_query *q, const cudasp_result *r, const cudasp_match_detail **details, uint32_t *n_details) {
+  if (!q || !r || !details || !n_details) return fail(q, CUDASP_ERR_ARG, "NULL argument");
+  Slot *s = slot_by_id(q, r->slot_id);
+  if (!s || s->state != 3) return fail(q, CUDASP_ERR_STATE, "result was not handed out");
+  if (!q->details_cap) return fail(q, CUDASP_ERR_STATE, "match details are not enabled: call cudasp_query_enable_details first");
+  *details = s->n_det ? reinterpret_cast<const cudasp_match_detail *>(s->h_det + 1) : nullptr;
+  *n_details = s->n_det;
+  return CUDASP_OK;
+}
+
+static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                           const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches,
+                           cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details) {
+  if (n_details) *n_details = 0;
+  uint32_t total_det = 0;
   if (key_format != CUDASP_KEYS_XY64 && key_format != CUDASP_KEYS_SEC1_33) return fail(q, CUDASP_ERR_ARG, "unknown key format");
   const size_t kb = key_bytes(key_format);
   if (!q || !n_matches) return fail(q, CUDASP_ERR_ARG, "NULL argument");
@@ -801,6 +907,13 @@ int cudasp_scan_batch_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_fo
     if (!r) {
       for (uint32_t i = 0; i < n; i++) match_ids[total + i] = p.base + p.s->h_result[1 + i];
       total += n;
+      if (n_details) {
+        for (uint32_t i = 0; i < p.s->n_det; i++, total_det++) {
+          if (total_det >= details_capacity) continue;       // counted, not stored
+          memcpy(&details[total_det], &p.s->h_det[1 + i], sizeof(cudasp_match_detail));
+          details[total_det].row += p.base;
+        }
+      }
     }
     release_slot(q, p.s);
     return r;
@@ -855,6 +968,10 @@ int cudasp_scan_batch_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_fo
     if (!rc) rc = r;
   }
   *n_matches = total;
+  if (n_details) {
+    *n_details = total_det;
+    if (!rc && total_det > details_capacity) rc = fail(q, CUDASP_ERR_ARG, "details capacity too small (n_details holds the number found)");
+  }
   if (trace)
     fprintf(stderr, "[cudasp] scan_batch %u rows: total %.3f ms, host copy %.3f, submit calls %.3f, waiting for the GPU %.3f\n", rows,
             1e3 * (now() - t_begin), 1e3 * t_copy, 1e3 * t_submit, 1e3 * t_wait);

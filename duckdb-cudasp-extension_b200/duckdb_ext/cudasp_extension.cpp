@@ -42,6 +42,7 @@ struct CudaspScanBindData : public TableFunctionData {
 	string label_keys;  // n_labels * 64 B, concatenated
 	uint32_t n_labels = 0;
 	idx_t batch_size = DEFAULT_BATCH;
+	bool details = false;  // details := true (extension): one result row per found output, + k, output_index, label_index, t_k
 };
 
 // Host-side columns of one submitted batch that never go to the GPU: only needed for matched rows.
@@ -77,6 +78,8 @@ struct CudaspScanState : public GlobalTableFunctionState {
 	vector<string> output_txids;
 	vector<int32_t> output_heights;
 	vector<string> output_tweak_keys;
+	bool details = false;
+	vector<cudasp_match_detail> output_details;  // details := true: parallel to the three vectors above
 	idx_t output_position = 0;
 };
 
@@ -176,8 +179,21 @@ static unique_ptr<FunctionData> CudaspScanBind(ClientContext &context, TableFunc
 		result->batch_size = (idx_t)v;
 	}
 
+	auto dt = input.named_parameters.find("details");
+	if (dt != input.named_parameters.end()) {
+		if (dt->second.type().id() != LogicalTypeId::BOOLEAN) {
+			throw InvalidInputException("details parameter must be a BOOLEAN");
+		}
+		result->details = !dt->second.IsNull() && dt->second.GetValue<bool>();
+	}
+
 	return_types = {LogicalType::BLOB, LogicalType::INTEGER, LogicalType::BLOB};
 	names = {"txid", "height", "tweak_key"};
+	if (result->details) {
+		// not in the reference: the BIP-352 k-loop on matching rows (include/cudasp.h, cudasp_match_detail)
+		return_types.insert(return_types.end(), {LogicalType::UINTEGER, LogicalType::UINTEGER, LogicalType::INTEGER, LogicalType::BLOB});
+		names.insert(names.end(), {"k", "output_index", "label_index", "t_k"});
+	}
 	return std::move(result);
 }
 
@@ -211,6 +227,10 @@ static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &contex
 		}
 		throw IOException("cudasp_scan: GPU initialisation failed: %s", msg ? msg : "unknown error");
 	}
+	state->details = bind.details;
+	if (bind.details && cudasp_query_enable_details(state->query, 0) != CUDASP_OK) {
+		ThrowGpu(*state, "cudasp_query_enable_details");
+	}
 	if (TraceOn()) {
 		fprintf(stderr, "[cudasp] query_create: %.3f s (%u slots/device, %d devices, %llu threads)\n", NowSec() - t_create, slots,
 		        n_dev, (unsigned long long)threads);
@@ -239,14 +259,23 @@ static void CollectResult(CudaspScanState &state, const cudasp_result &r) {
 		meta = std::move(it->second);
 		state.inflight.erase(it);
 	}
-	if (r.n_matches) {
+	const cudasp_match_detail *det = nullptr;
+	uint32_t n_det = 0;
+	if (state.details && cudasp_result_details(state.query, &r, &det, &n_det) != CUDASP_OK) {
+		ThrowGpu(state, "cudasp_result_details");
+	}
+	const uint32_t n_rows_out = state.details ? n_det : r.n_matches;
+	if (n_rows_out) {
 		std::lock_guard<std::mutex> guard(state.output_lock);
-		for (uint32_t k = 0; k < r.n_matches; k++) {
-			const uint32_t i = r.match_ids[k];
+		for (uint32_t k = 0; k < n_rows_out; k++) {
+			const uint32_t i = state.details ? det[k].row : r.match_ids[k];
 			const uint32_t b = i ? meta->txid_end[i - 1] : 0, e = meta->txid_end[i];
 			state.output_txids.emplace_back(meta->txid_bytes.data() + b, e - b);
 			state.output_heights.push_back(meta->heights[i]);
 			state.output_tweak_keys.emplace_back(const_char_ptr_cast(meta->tweak_keys) + (size_t)i * meta->key_bytes, meta->key_bytes);
+			if (state.details) {
+				state.output_details.push_back(det[k]);
+			}
 		}
 	}
 	if (cudasp_release_result(state.query, &r) != CUDASP_OK) {
@@ -481,6 +510,19 @@ static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &cont
 			height_out[i] = state.output_heights[src];
 			tweak_out[i] = StringVector::AddStringOrBlob(output.data[2], state.output_tweak_keys[src]);
 		}
+		if (state.details) {
+			auto k_out = FlatVector::GetData<uint32_t>(output.data[3]);
+			auto oi_out = FlatVector::GetData<uint32_t>(output.data[4]);
+			auto li_out = FlatVector::GetData<int32_t>(output.data[5]);
+			auto t_out = FlatVector::GetData<string_t>(output.data[6]);
+			for (idx_t i = 0; i < n; i++) {
+				const cudasp_match_detail &d = state.output_details[state.output_position + i];
+				k_out[i] = d.k;
+				oi_out[i] = d.output_index;
+				li_out[i] = d.label_index;
+				t_out[i] = StringVector::AddStringOrBlob(output.data[6], const_char_ptr_cast(d.t_k), 32);
+			}
+		}
 		output.SetCardinality(n);
 		state.output_position += n;
 	}
@@ -496,6 +538,7 @@ static void LoadInternal(ExtensionLoader &loader) {
 	func.in_out_function = CudaspScanFunction;
 	func.in_out_function_final = CudaspScanFinalFunction;
 	func.named_parameters["batch_size"] = LogicalType::INTEGER;
+	func.named_parameters["details"] = LogicalType::BOOLEAN;
 	loader.RegisterFunction(func);
 }
 

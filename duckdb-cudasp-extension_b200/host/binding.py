@@ -30,6 +30,11 @@ class Result(C.Structure):
                 ("match_ids", u32p)]
 
 
+class MatchDetail(C.Structure):      # include/cudasp.h cudasp_match_detail
+    _fields_ = [("row", C.c_uint32), ("k", C.c_uint32), ("output_index", C.c_uint32), ("label_index", C.c_int32),
+                ("t_k", C.c_uint8 * 32)]
+
+
 KEYS_XY64, KEYS_SEC1_33 = 0, 1          # include/cudasp.h CUDASP_KEYS_*
 KEY_BYTES = {KEYS_XY64: 64, KEYS_SEC1_33: 33}
 
@@ -37,7 +42,8 @@ EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "c
            "cudasp_acquire_slot", "cudasp_submit_slot", "cudasp_poll", "cudasp_wait", "cudasp_release_result",
            "cudasp_scan_device", "cudasp_profile_stages", "cudasp_scan_candidates", "cudasp_scan_intermediates", "cudasp_test_field",
            "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory",
-           "cudasp_scan_batch_fmt", "cudasp_submit_slot_fmt", "cudasp_scan_candidates_fmt"]
+           "cudasp_scan_batch_fmt", "cudasp_submit_slot_fmt", "cudasp_scan_candidates_fmt",
+           "cudasp_query_enable_details", "cudasp_result_details", "cudasp_scan_batch_details"]
 
 
 def lib():
@@ -66,6 +72,9 @@ def lib():
         L.cudasp_scan_batch_fmt.argtypes = [vp, vp, C.c_int, vp, vp, C.c_uint32, vp, u32p]
         L.cudasp_submit_slot_fmt.argtypes = [vp, C.POINTER(Slot), C.c_uint32, C.c_uint64, C.c_uint64, C.c_int]
         L.cudasp_scan_candidates_fmt.argtypes = [vp, vp, C.c_int, C.c_uint32, vp, vp]
+        L.cudasp_query_enable_details.argtypes = [vp, C.c_uint32]
+        L.cudasp_result_details.argtypes = [vp, C.POINTER(Result), C.POINTER(C.POINTER(MatchDetail)), u32p]
+        L.cudasp_scan_batch_details.argtypes = [vp, vp, C.c_int, vp, vp, C.c_uint32, vp, u32p, C.POINTER(MatchDetail), C.c_uint32, u32p]
         L.cudasp_scan_intermediates.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
         L.cudasp_test_field.argtypes = [C.c_int, C.c_int, vp, vp, vp, C.c_uint32]
         L.cudasp_launch_count.argtypes = [vp]
@@ -158,6 +167,28 @@ class Query:
             self._check(lib().cudasp_scan_batch_fmt(self._h, _ptr(tweaks), key_format, outp, _ptr(out_offsets), rows, _ptr(ids),
                                                     C.byref(n)))
         return ids[: n.value].copy()
+
+    def enable_details(self, max_details_per_batch: int = 0):
+        """Opt in to the BIP-352 k-loop on matching rows (include/cudasp.h, match details); before the first batch."""
+        self._check(lib().cudasp_query_enable_details(self._h, max_details_per_batch))
+        self.details_enabled = True
+
+    def scan_batch_details(self, tweaks: np.ndarray, outputs: np.ndarray, out_offsets: np.ndarray, key_format: int = KEYS_XY64,
+                           capacity: Optional[int] = None):
+        """-> (ascending matching row ids, [(row, k, output_index, label_index, t_k int)] sorted by (row, k))."""
+        tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, KEY_BYTES[key_format])
+        rows = tweaks.shape[0]
+        out_offsets = np.ascontiguousarray(out_offsets, dtype=np.uint32)
+        assert out_offsets.shape[0] == rows + 1
+        outputs = np.ascontiguousarray(outputs if outputs is not None else np.zeros(0, np.int64), dtype=np.int64)
+        ids = np.zeros(max(rows, 1), np.uint32)
+        cap = capacity if capacity is not None else max(rows, 1)
+        det = (MatchDetail * max(cap, 1))()
+        n, nd = C.c_uint32(0), C.c_uint32(0)
+        self._check(lib().cudasp_scan_batch_details(self._h, _ptr(tweaks), key_format, _ptr(outputs), _ptr(out_offsets), rows, _ptr(ids),
+                                                    C.byref(n), det, cap, C.byref(nd)))
+        recs = [(d.row, d.k, d.output_index, d.label_index, int.from_bytes(bytes(d.t_k), "big")) for d in det[: nd.value]]
+        return ids[: n.value].copy(), recs
 
     def candidates(self, tweaks: np.ndarray, key_format: int = KEYS_XY64, with_valid: bool = False):
         tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, KEY_BYTES[key_format])

@@ -33,13 +33,19 @@ class IOException(RuntimeError):
 
 
 class CudaspScanBindData:
-    def __init__(self, scan_private_key: bytes, spend_public_key: bytes, label_keys: List[bytes], batch_size: int):
+    def __init__(self, scan_private_key: bytes, spend_public_key: bytes, label_keys: List[bytes], batch_size: int,
+                 details: bool = False):
         self.scan_private_key_data = scan_private_key
         self.spend_public_key_data = spend_public_key
         self.label_keys_data = label_keys
         self.batch_size = batch_size
+        self.details = details
         self.return_types = ["BLOB", "INTEGER", "BLOB"]
         self.names = ["txid", "height", "tweak_key"]
+        if details:
+            # extension (SURVEY.md 8f rank 3+4): one result row per found output instead of one per transaction
+            self.return_types += ["UINTEGER", "UINTEGER", "INTEGER", "BLOB"]
+            self.names += ["k", "output_index", "label_index", "t_k"]
 
 
 def CudaspScanBind(inputs: Sequence, named_parameters: Optional[dict] = None) -> CudaspScanBindData:
@@ -75,7 +81,12 @@ def CudaspScanBind(inputs: Sequence, named_parameters: Optional[dict] = None) ->
         if v > 10000000:
             raise InvalidInputException("batch_size too large (max 10,000,000), got %d" % v)
         batch_size = int(v)
-    return CudaspScanBindData(bytes(scan_private_key), bytes(spend_public_key), labels, batch_size)
+    details = False
+    if "details" in named_parameters:
+        if not isinstance(named_parameters["details"], (bool, np.bool_)):
+            raise InvalidInputException("details parameter must be a BOOLEAN")
+        details = bool(named_parameters["details"])
+    return CudaspScanBindData(bytes(scan_private_key), bytes(spend_public_key), labels, batch_size, details)
 
 
 class CudaspScanLocalState:
@@ -97,8 +108,11 @@ class CudaspScanState:
         try:
             self.query = Query(bind_data.scan_private_key_data, bind_data.spend_public_key_data, bind_data.label_keys_data,
                                devices=devices, batch_rows=bind_data.batch_size)
+            if bind_data.details:
+                self.query.enable_details()
         except CudaspError as e:
             raise IOException(str(e))
+        self.output_details: List[Tuple] = []      # details := true: (k, output_index, label_index, t_k) per result row
         self.output_txids: List[bytes] = []
         self.output_heights: List[int] = []
         self.output_tweak_keys: List[bytes] = []
@@ -134,6 +148,7 @@ def ProcessBatch(local_state: CudaspScanLocalState, bind_data: CudaspScanBindDat
     outs = np.array(local_state.accumulated_outputs, dtype=np.int64)
     lens = np.fromiter((len(t) for t in local_state.accumulated_tweak_keys), dtype=np.int64, count=n)
     matched: List[int] = []
+    details = {}                                   # source row -> [(k, output_index, label_index, t_k)]
     for size, fmt in ((TWEAK_KEY_SIZE, KEYS_XY64), (COMPRESSED_KEY_SIZE, KEYS_SEC1_33)):
         sel = np.nonzero(lens == size)[0]
         if len(sel) == 0:
@@ -146,14 +161,22 @@ def ProcessBatch(local_state: CudaspScanLocalState, bind_data: CudaspScanBindDat
             sub_off = np.concatenate([[0], np.cumsum(cnt)])
             sub_out = np.concatenate([outs[offs[i]: offs[i + 1]] for i in sel]) if len(sel) else outs[:0]
         try:
-            ids = global_state.query.scan_batch(tw, sub_out, sub_off.astype(np.uint32), key_format=fmt)
+            if bind_data.details:
+                ids, recs = global_state.query.scan_batch_details(tw, sub_out, sub_off.astype(np.uint32), key_format=fmt)
+                for row, k, oi, li, t in recs:
+                    details.setdefault(int(sel[row]), []).append((k, oi, li, t.to_bytes(32, "big")))
+            else:
+                ids = global_state.query.scan_batch(tw, sub_out, sub_off.astype(np.uint32), key_format=fmt)
         except CudaspError as e:
             raise IOException(str(e))
         matched.extend(int(sel[i]) for i in ids.tolist())
     for i in sorted(matched):
-        global_state.output_txids.append(local_state.accumulated_txids[i])
-        global_state.output_heights.append(local_state.accumulated_heights[i])
-        global_state.output_tweak_keys.append(local_state.accumulated_tweak_keys[i])
+        for rec in (details.get(i, []) if bind_data.details else [None]):
+            global_state.output_txids.append(local_state.accumulated_txids[i])
+            global_state.output_heights.append(local_state.accumulated_heights[i])
+            global_state.output_tweak_keys.append(local_state.accumulated_tweak_keys[i])
+            if rec is not None:
+                global_state.output_details.append(rec)
     local_state.__init__()
 
 
@@ -175,7 +198,10 @@ def CudaspScanFinalFunction(bind_data, global_state, local_state):
         a = global_state.output_position
         b = min(a + STANDARD_VECTOR_SIZE, len(global_state.output_txids))
         global_state.output_position = b
-        yield list(zip(global_state.output_txids[a:b], global_state.output_heights[a:b], global_state.output_tweak_keys[a:b]))
+        base = list(zip(global_state.output_txids[a:b], global_state.output_heights[a:b], global_state.output_tweak_keys[a:b]))
+        if bind_data.details:
+            base = [r + d for r, d in zip(base, global_state.output_details[a:b])]
+        yield base
 
 
 def cudasp_scan(rows: Iterable[Tuple], scan_private_key, spend_public_key, label_keys, devices=None, **named_parameters):

@@ -147,6 +147,30 @@ int cudasp_profile_stages(cudasp_query *q, int device, const uint8_t *d_tweak_ke
                           const uint32_t *d_out_offsets, uint32_t rows, uint32_t *d_match_ids, uint32_t *d_n_matches,
                           float *stage_ms);
 
+/* ---- match details: the full BIP-352 receive loop on the rows that matched (extension, opt-in) ----------------
+ * The reference stops at "this row has an output of mine": k = 0 only, no word on which output, which label, or the
+ * tweak needed to spend (/root/reference/src/cudasp_gpu.cu:278-282, src/cudasp_extension.cu:383-391).  With details
+ * enabled, every matching row is followed through BIP-352's scanning loop on the GPU (one extra kernel over the
+ * handful of matched rows): k = 0, 1, 2, ... while an output equals P_k or P_k + label_i (64-bit x prefixes, the
+ * reference's data model), t_k range-checked (0 < t_k < n).  match_ids are NOT affected: they stay bit-exact with the
+ * reference; details only add information about those rows. */
+typedef struct cudasp_match_detail {
+  uint32_t row;          /* row id within the batch (cudasp_scan_batch_details: within the call) */
+  uint32_t k;            /* BIP-352 output counter */
+  uint32_t output_index; /* position in the row's outputs list (NULL children not counted) */
+  int32_t label_index;   /* -1: P_k itself; i >= 0: P_k + label_keys[i] */
+  uint8_t t_k[32];       /* big-endian; the output's private key is b_spend + t_k (+ the label's scalar) mod n */
+} cudasp_match_detail;
+
+/* Call after create, before the first batch.  max_details_per_batch = 0 picks min(batch_rows, 65536). */
+int cudasp_query_enable_details(cudasp_query *q, uint32_t max_details_per_batch);
+/* Details of a result handed out by cudasp_poll / cudasp_wait, sorted by (row, k); valid until the result is released. */
+int cudasp_result_details(cudasp_query *q, const cudasp_result *r, const cudasp_match_detail **details, uint32_t *n_details);
+/* cudasp_scan_batch_fmt plus details (rows numbered over the whole call). */
+int cudasp_scan_batch_details(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                              const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches,
+                              cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details);
+
 /* ---- introspection used by the parity tests and bench.py -----------------------------------
  * Per-row candidates instead of match flags: cands[r*(1+L) + 0] = base, [.. + 1 + i] = label i. */
 int cudasp_scan_candidates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, int64_t *cands);

@@ -118,6 +118,27 @@ def decompress(sec1: bytes):
     return bool(ok), out.tobytes()
 
 
+def details_row(sk, spend, labels, S_le, outputs, cap=64):
+    """-> [(k, output_index, label_index, t_k int)] from the product's details_row (K8 body) on the CPU."""
+    lib = load()
+    lab = _b(b"".join(labels)) if labels else np.zeros(1, np.uint8)
+    outs = np.ascontiguousarray(outputs, dtype=np.int64) if len(outputs) else np.zeros(1, np.int64)
+    out = np.zeros(44 * cap, np.uint8)
+    n = lib.hc_details_row(_p(_b(sk)), _p(_b(spend)), _p(lab), len(labels), _p(_b(S_le)), outs.ctypes.data_as(C.POINTER(C.c_int64)),
+                           len(outputs), _p(out), cap)
+    assert n >= 0, n
+    res = []
+    for i in range(n):
+        rec = out[44 * i: 44 * i + 44]
+        k, oi, li = np.frombuffer(rec[:12].tobytes(), np.int32).tolist()
+        res.append((k, oi, li, int.from_bytes(rec[12:].tobytes(), "big")))
+    return res
+
+
+def tweak_in_range(t: int) -> bool:
+    return bool(load().hc_tweak_in_range(_p(_b(t.to_bytes(32, "little")))))
+
+
 def gtab_shape():
     lib = load()
     a, b = C.c_int(), C.c_int()

@@ -6,6 +6,7 @@
 // against the oracle.  It is never linked into libcudasp_b200.so and is not a CPU fallback.
 #include <stdint.h>
 #include <string.h>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -162,6 +163,35 @@ int hc_scan_candidates(const uint8_t sk[32], const uint8_t spend[64], const uint
   }
   return 0;
 }
+
+// details_row (the K8 body) for one row given its affine shared secret; out: n records of
+// {k, output_index, label_index, t_k[32] BE} = 3 x int32 + 32 bytes = 44 bytes each.  Returns the count.
+int hc_details_row(const uint8_t sk[32], const uint8_t spend[64], const uint8_t *labels, uint32_t L, const uint8_t S_le[64],
+                   const int64_t *outputs, uint32_t n_out, uint8_t *out, uint32_t cap) {
+  QueryPlan q;
+  std::string err;
+  int rc = make_query_plan(q, sk, spend, labels, L, err);
+  if (rc) return rc;
+  const GTabHost &g = gtab_host();
+  fe sx, sy;
+  fe_from_le_bytes(sx, S_le);
+  fe_from_le_bytes(sy, S_le + 32);
+  uint32_t n = 0;
+  details_row(sx, sy.v[0] & 1u, outputs, 0u, n_out, q.labels.data(), L, g.table.data(), q.fp,
+              [&](uint32_t k, uint32_t oi, int32_t li, const fe &t) {
+                if (n >= cap) return;
+                uint8_t *o = out + 44 * (size_t)n++;
+                int32_t h[3] = {(int32_t)k, (int32_t)oi, li};
+                memcpy(o, h, 12);
+                for (int l = 0; l < 8; l++) {
+                  uint32_t wv = t.v[7 - l];
+                  o[12 + 4 * l] = (uint8_t)(wv >> 24); o[13 + 4 * l] = (uint8_t)(wv >> 16);
+                  o[14 + 4 * l] = (uint8_t)(wv >> 8); o[15 + 4 * l] = (uint8_t)wv;
+                }
+              });
+  return (int)n;
+}
+int hc_tweak_in_range(const uint8_t t_le[32]) { fe t; fe_from_le_bytes(t, t_le); return tweak_in_range(t) ? 1 : 0; }
 
 // gtab[w][d] as 64 B LE
 void hc_gtab_entry(int w, int d, uint8_t out[64]) {

@@ -64,3 +64,23 @@ def make_table(rows: int, seed: int, n_labels: int = 0, n_base: int = 100, n_per
             outputs[slot] = cands[len(planted) + j, 0] ^ 1     # low bit flipped: must NOT match
     return dict(sk=sk, spend=spend, labels=labels, tweaks=tweaks, outputs=outputs, offsets=offsets,
                 expected=np.array(sorted(expected), dtype=np.uint32))
+
+
+def sender_outputs(sk: bytes, spend: bytes, labels, tweak: bytes, recipe, rng=None):
+    """Sender side of BIP-352 for ONE transaction (test infrastructure, uses the oracle's EC arithmetic): the list of
+    64-bit output prefixes a sender would create paying this recipient len(recipe) times, recipe[k] = -1 (B_spend) or a
+    label index, with k counting up from 0 -- plus the expected receiver records [(k, label, t_k)].
+    P_k = B_m + t_k*G with t_k = hash(ser(S) || ser32(k)), S = scan_sk * tweak (= a_sum*input_hash * B_scan on the
+    sender's side; the same point)."""
+    from oracle import ref_scan as R
+    S = R.pt_mul(R.parse_scalar(sk), R.parse_point(tweak))
+    B = R.parse_point(spend)
+    outs, recs = [], []
+    for k, m in enumerate(recipe):
+        msg = bytes([0x02 + (S[1] & 1)]) + S[0].to_bytes(32, "big") + k.to_bytes(4, "big")
+        t = int.from_bytes(R.tagged_hash(msg), "big")
+        Bm = B if m < 0 else R.pt_add(B, R.parse_point(labels[m]))
+        Pk = R.pt_add(R.pt_mul(t, R.G), Bm)
+        outs.append(R.upper64_signed(Pk[0]))
+        recs.append((k, m, t))
+    return outs, recs

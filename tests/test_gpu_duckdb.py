@@ -153,3 +153,33 @@ def test_compressed_tweak_keys_through_duckdb(tmp_path, mode, threads):
     want = sorted((txids[i].hex().upper(), heights[i], tweaks[i].hex().upper()) for i in expected)
     got = sorted((a, int(b), c) for a, b, c in (ln.split(",") for ln in lines))
     assert got == want
+
+
+def test_details_parameter_through_duckdb(tmp_path):
+    """details := true (extension): one result row per found output with k, output_index, label_index and t_k; the
+    default call on the same table still returns the reference's three columns, one row per transaction."""
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    from tests.test_gpu_details import build_table
+    rows = 6000
+    T, want = build_table(rows, 2, 31415, 40)
+    txids = [i.to_bytes(4, "little") * 8 for i in range(rows)]
+    tbl = pa.table({"txid": pa.array(txids, pa.binary()), "height": pa.array([800000 + i for i in range(rows)], pa.int32()),
+                    "tweak_key": pa.array([T["tweaks"][i].tobytes() for i in range(rows)], pa.binary()),
+                    "outputs": pa.array(T["lists"], pa.list_(pa.int64()))})
+    path = str(tmp_path / "d.parquet")
+    pq.write_table(tbl, path, row_group_size=1500)
+    q = dict(scan_sk=T["sk"].hex(), spend=T["spend"].hex(), labels=[l.hex() for l in T["labels"]], batch_size=1000)
+    call = scan_call("read_parquet('%s')" % path, q)
+    rc, lines, err = run_sql("SELECT height, k, output_index, label_index, hex(t_k) FROM %s ORDER BY 1, 2;" % call.replace(
+        "batch_size := 1000", "batch_size := 1000, details := true"), threads=4)
+    assert rc == 0, err
+    got = [tuple(ln.split(",")) for ln in lines]
+    exp = sorted((800000 + r, k, oi, li, "%064X" % t) for r, recs in want.items() for k, oi, li, t in recs)
+    assert [(int(a), int(b), int(c), int(d), e) for a, b, c, d, e in got] == exp
+    rc, lines, err = run_sql("SELECT height FROM %s ORDER BY 1;" % call, threads=4)
+    assert rc == 0, err
+    assert [int(x) for x in lines] == sorted(800000 + r for r in want)
+    # details := false is the default schema
+    rc, lines, err = run_sql("SELECT count(*) FROM %s;" % call.replace("batch_size := 1000", "details := false"), threads=2)
+    assert rc == 0 and int(lines[0]) == len(want), err

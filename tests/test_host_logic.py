@@ -208,3 +208,46 @@ def test_decompress_tweak_row_function():
         assert ok == valid == (R.decompress_sec1(blob) is not None)
         if valid:
             assert R.parse_point(out) == g
+
+
+def test_details_row_follows_bip352_k_loop():
+    """K8 body (details_row) on the CPU against the oracle's receive_scan_row, on transactions built by a sender-side
+    generator: several outputs to one recipient (k = 0..3), labels, shuffled output order, foreign outputs, a gap
+    (k = 0 and k = 2 present, k = 1 missing: the loop must stop after k = 0)."""
+    import random
+    from tests import synth
+    rng = random.Random(77)
+    sk, spend, labels = synth.make_keys(21, 3)
+    g = R.encode_point(R.G)
+    for case, recipe in enumerate([[-1], [0], [-1, -1, 2, 1], [2, 2, -1], [-1, 0, 1, 2, -1]]):
+        tweak = R.encode_point(R.pt_mul(1000 + case, R.G))
+        outs, recs = synth.sender_outputs(sk, spend, labels, tweak, recipe)
+        foreign = [rng.getrandbits(63) for _ in range(3)]
+        mixed = outs + foreign
+        order = list(range(len(mixed)))
+        rng.shuffle(order)
+        shuffled = [mixed[i] for i in order]
+        S = R.pt_mul(R.parse_scalar(sk), R.parse_point(tweak))
+        want = R.receive_scan_row(R.parse_scalar(sk), R.parse_point(tweak), R.parse_point(spend), [R.parse_point(l) for l in labels], shuffled)
+        got = H.details_row(sk, spend, labels, R.encode_point(S), shuffled)
+        assert got == want
+        # and it is what the sender intended: record k sits where output k went, with the sender's t_k and label
+        assert [(k, shuffled[oi], li, t) for k, oi, li, t in got] == [(k, outs[k], m, t) for k, m, t in recs]
+        # spendability: (b_spend + t_k + label scalar)*G has the output's x prefix -- checked through B_m + t_k*G
+        for k, oi, li, t in got:
+            Bm = R.parse_point(spend) if li < 0 else R.pt_add(R.parse_point(spend), R.parse_point(labels[li]))
+            assert R.upper64_signed(R.pt_add(R.pt_mul(t, R.G), Bm)[0]) == shuffled[oi]
+    # a gap in k stops the loop
+    tweak = R.encode_point(R.pt_mul(4242, R.G))
+    outs, recs = synth.sender_outputs(sk, spend, labels, tweak, [-1, -1, -1])
+    S = R.encode_point(R.pt_mul(R.parse_scalar(sk), R.parse_point(tweak)))
+    got = H.details_row(sk, spend, labels, S, [outs[2], outs[0]])
+    assert [(k, oi) for k, oi, _, _ in got] == [(0, 1)]
+    assert H.details_row(sk, spend, labels, S, [outs[1], 5]) == []          # no k = 0 output: nothing
+    assert H.details_row(sk, spend, labels, S, []) == []
+    # duplicates: the same prefix twice is consumed once per k
+    got = H.details_row(sk, spend, labels, S, [outs[0], outs[0], outs[1]])
+    assert [(k, oi) for k, oi, _, _ in got] == [(0, 0), (1, 2)]
+    # range check of t_k
+    assert H.tweak_in_range(1) and H.tweak_in_range(R.N - 1)
+    assert not H.tweak_in_range(0) and not H.tweak_in_range(R.N) and not H.tweak_in_range(2**256 - 1)
