@@ -354,6 +354,7 @@ struct MatchDetail {           // == cudasp_match_detail (include/cudasp.h)
   int32_t label_index;
   uint8_t t_k[32];
 };
+static const uint32_t DETAILS_MAX_LABELS = 64;   // == CUDASP_MAX_LABELS
 static const uint32_t DETAILS_MAX_K = 32;      // more outputs to one recipient in one transaction than this are not followed
 
 CSP_HD bool tweak_in_range(const fe &t) {      // 0 < t < n  (n = group order)
@@ -383,6 +384,19 @@ CSP_HD uint32_t details_row(const fe &sx, uint32_t s_odd, const int64_t *outputs
     fe zi, x0, y0;
     fe_inv(zi, acc.z);
     const int64_t c0 = base_candidate(x0, &y0, acc.x, acc.y, zi);
+    // the candidates of this k once (they do not depend on the output): c[0] = P_k, c[1 + i] = P_k + L_i, same rule
+    // as K5/K7 (label_candidate) with a private inversion per label
+    int64_t c[1 + DETAILS_MAX_LABELS];
+    c[0] = c0;
+    for (uint32_t i = 0; i < n_labels; i++) {
+      fe lx, ly, d;
+      load_fe_ro(lx, &labels[i].x);
+      load_fe_ro(ly, &labels[i].y);
+      fe_sub(d, lx, x0);
+      fe_normalize(d);
+      if (!fe_is_zero(d)) fe_inv(d, d);
+      c[1 + i] = label_candidate(x0, y0, lx, ly, d);
+    }
     int32_t hit_label = -2;
     uint32_t hit_out = 0;
     // outputs in list order; for each, P_k itself first, then the labels in order (BIP-352 "Scanning")
@@ -391,16 +405,8 @@ CSP_HD uint32_t details_row(const fe &sx, uint32_t s_odd, const int64_t *outputs
       for (uint32_t u = 0; u < found; u++) gone |= used[u] == j;
       if (gone) continue;
       const int64_t o = outputs[j];
-      if (o == c0) { hit_label = -1; hit_out = j; break; }
-      for (uint32_t i = 0; i < n_labels; i++) {
-        fe lx, ly, d;
-        load_fe_ro(lx, &labels[i].x);
-        load_fe_ro(ly, &labels[i].y);
-        fe_sub(d, lx, x0);                     // same candidate rule as K5/K7 (label_candidate), private inversion
-        fe_normalize(d);
-        if (!fe_is_zero(d)) fe_inv(d, d);
-        const int64_t c = label_candidate(x0, y0, lx, ly, d);
-        if (o == c) { hit_label = (int32_t)i; hit_out = j; break; }
+      for (uint32_t i = 0; i <= n_labels; i++) {
+        if (o == c[i]) { hit_label = (int32_t)i - 1; hit_out = j; break; }
       }
     }
     if (hit_label == -2) break;

@@ -35,6 +35,7 @@ class MatchDetail(C.Structure):      # include/cudasp.h cudasp_match_detail
                 ("t_k", C.c_uint8 * 32)]
 
 
+DETAIL_DTYPE = np.dtype([("row", "<u4"), ("k", "<u4"), ("output_index", "<u4"), ("label_index", "<i4"), ("t_k", "V32")])
 KEYS_XY64, KEYS_SEC1_33 = 0, 1          # include/cudasp.h CUDASP_KEYS_*
 KEY_BYTES = {KEYS_XY64: 64, KEYS_SEC1_33: 33}
 
@@ -182,12 +183,20 @@ class Query:
         assert out_offsets.shape[0] == rows + 1
         outputs = np.ascontiguousarray(outputs if outputs is not None else np.zeros(0, np.int64), dtype=np.int64)
         ids = np.zeros(max(rows, 1), np.uint32)
-        cap = capacity if capacity is not None else max(rows, 1)
-        det = (MatchDetail * max(cap, 1))()
+        cap = capacity if capacity is not None else min(max(rows, 1), 4096)
         n, nd = C.c_uint32(0), C.c_uint32(0)
-        self._check(lib().cudasp_scan_batch_details(self._h, _ptr(tweaks), key_format, _ptr(outputs), _ptr(out_offsets), rows, _ptr(ids),
-                                                    C.byref(n), det, cap, C.byref(nd)))
-        recs = [(d.row, d.k, d.output_index, d.label_index, int.from_bytes(bytes(d.t_k), "big")) for d in det[: nd.value]]
+        while True:
+            det = (MatchDetail * max(cap, 1))()
+            rc = lib().cudasp_scan_batch_details(self._h, _ptr(tweaks), key_format, _ptr(outputs), _ptr(out_offsets), rows, _ptr(ids),
+                                                 C.byref(n), det, cap, C.byref(nd))
+            if rc == ERR_ARG and capacity is None and nd.value > cap:      # more records than guessed: n_details says how many
+                cap = nd.value
+                continue
+            self._check(rc)
+            break
+        a = np.frombuffer(det, dtype=DETAIL_DTYPE, count=nd.value)
+        recs = list(zip(a["row"].tolist(), a["k"].tolist(), a["output_index"].tolist(), a["label_index"].tolist(),
+                        [int.from_bytes(t.tobytes(), "big") for t in a["t_k"]]))
         return ids[: n.value].copy(), recs
 
     def candidates(self, tweaks: np.ndarray, key_format: int = KEYS_XY64, with_valid: bool = False):
