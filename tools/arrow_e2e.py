@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--labels", type=int, default=0)
     ap.add_argument("--batch", type=int, default=300000)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--devices", type=int, default=1, help="GPUs owned by the one query handle (one feeding thread)")
     ap.add_argument("--chunk", type=int, default=122880, help="rows per record batch / Parquet row group")
     a = ap.parse_args()
     import numpy as np
@@ -35,9 +36,9 @@ def main():
     M = cudasp_b200_loader.load()
     T = synth.make_table(a.rows, 352004, n_labels=a.labels, n_base=100, n_per_label=100 if a.labels else 0, batch_rows=a.batch)
     want = T["expected"].astype(np.uint64)
-    res = {"rows": a.rows, "labels": a.labels, "chunk": a.chunk}
+    res = {"rows": a.rows, "labels": a.labels, "chunk": a.chunk, "devices": a.devices}
     d = tempfile.mkdtemp(prefix="cudasp_arrow_")
-    with M.Query(T["sk"], T["spend"], T["labels"], devices=[0], batch_rows=a.batch) as q:
+    with M.Query(T["sk"], T["spend"], T["labels"], devices=list(range(a.devices)), batch_rows=a.batch) as q:
         for name, tbl in (("xy64", arrow_table(T)), ("sec1", arrow_table(T, compress(T["tweaks"]), 33))):
             tbl = pa.Table.from_batches(tbl.to_batches(max_chunksize=a.chunk))
             best = None
