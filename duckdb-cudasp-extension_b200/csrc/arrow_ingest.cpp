@@ -5,6 +5,7 @@
 // Two staging paths per piece (a piece = up to piece_rows rows, whole K1 waves):
 //   dense   : no NULL keys / lists / children in sight and one key width -> memcpy(keys), rebase(offsets), memcpy(values)
 //   general : row by row with the reference's NULL rules, rows compacted, a row map kept to translate ids back
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <deque>
@@ -117,7 +118,9 @@ int format_of(int64_t key_size) {
 // row numbers (row_base + index in the pair), ascending per pair, pairs in push order.
 class ArrowScanner {
  public:
-  explicit ArrowScanner(cudasp_query *q) : q_(q), piece_(stg::piece_rows(q)) {}
+  explicit ArrowScanner(cudasp_query *q) : q_(q), piece_(stg::piece_rows(q)) {
+    cur_ = std::min(piece_, std::max<uint32_t>(piece_ / 8, 8192u));     // ramp-up: see piece_now()
+  }
   ~ArrowScanner() {
     for (Pending &p : pending_) {        // error exit: let the slot's stream finish before its staging is reused
       uint32_t n = 0;
@@ -160,7 +163,13 @@ class ArrowScanner {
 
   cudasp_query *q_;
   uint32_t piece_;
+  uint32_t cur_ = 0;
   std::deque<Pending> pending_;
+
+  // rows for the next piece: the first pieces of a scan ramp up (1/8, 1/4, 1/2 of a full piece) so that the GPU starts
+  // after a short host copy instead of idling through a full one
+  uint32_t piece_now() const { return cur_; }
+  void piece_done() { cur_ = (uint32_t)std::min<uint64_t>(piece_, 2ull * cur_); }
 
   static bool dense_ok(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity) {
     return !row_validity && !k.may_have_nulls && !l.may_have_nulls && !l.child_may_have_nulls;
@@ -198,10 +207,10 @@ class ArrowScanner {
   // returns 0 = staged a piece (*a advanced), 1 = this piece needs the general path, < 0 = error
   int stage_dense(const KeyColumn &k, const ListColumn &l, uint64_t row_base, int64_t *a) {
     const int64_t base = *a;
-    const int64_t cnt = std::min<int64_t>(piece_, k.length - base);
     const int64_t w = k.size(base);
     const int fmt = format_of(w);
     if (fmt < 0) return 1;
+    const int64_t cnt = std::min<int64_t>(piece_now(), k.length - base);
     if (!k.width) {                   // binary column: the piece must be one uniform width
       bool uniform = true;
       if (k.large) {
@@ -238,6 +247,7 @@ class ArrowScanner {
       return rc;
     }
     pending_.push_back(Pending{s, row_base + (uint64_t)base, {}});
+    piece_done();
     *a = base + cnt;
     return 0;
   }
@@ -268,7 +278,7 @@ int ArrowScanner::stage_general(const KeyColumn &k, const ListColumn &l, const u
   int rc = acquire(&s);
   if (rc) return rc;
   Pending p{s, row_base + (uint64_t)first, {}};
-  const uint32_t cap = std::min<uint32_t>(piece_, p.s.cap_rows);
+  const uint32_t cap = std::min<uint32_t>(piece_now(), p.s.cap_rows);
   p.rowmap.reserve(cap);
   uint32_t rows = 0;
   uint64_t n_out = 0;
@@ -315,6 +325,7 @@ int ArrowScanner::stage_general(const KeyColumn &k, const ListColumn &l, const u
     return rc;
   }
   pending_.push_back(std::move(p));
+  piece_done();
   return 0;
 }
 

@@ -37,6 +37,7 @@ const int SLOTS_PER_DEVICE = 6, MAX_SLOTS_PER_DEVICE = 64;   // 6: measured, a 3
 const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
 const uint32_t EAGER_DETAILS = 32; // detail records copied back together with their count
 const uint32_t DETAILS_GRID = 64;  // K8: 64 one-warp blocks stride over the matched rows
+const uint32_t RAMP_DIV = 8;               // ... starting with 1/8 of a piece, doubling (see scan_batch_impl)
 const uint32_t SYNC_PIECE_WAVES = 2;       // cudasp_scan_batch streams a large call in pieces of this many K1 waves
 const int LADDER_BLOCK = 128, LADDER_MINB = 3;
 const int HASH_BLOCK = 128, HASH_MINB = 3;
@@ -920,9 +921,12 @@ static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_f
   };
   // Pieces smaller than batch_rows: the first H2D copy is short, so the GPU starts early, and the memcpy of
   // piece k+1 into pinned memory overlaps the kernels of piece k (separate slots, separate streams).
+  // The first pieces ramp up (1/8, 1/4, 1/2 of a full piece): the host copy of a full first piece would leave the GPU
+  // idle for ~1.5 ms at the start of every call.
   const uint32_t piece = std::min<uint32_t>(q->batch_rows, q->piece_rows);
-  for (uint32_t base = 0; base < rows && !rc; base += piece) {
-    const uint32_t cnt = std::min<uint32_t>(piece, rows - base);
+  uint32_t cur = std::min(piece, std::max<uint32_t>(piece / RAMP_DIV, 8192u));
+  for (uint32_t base = 0, cnt = 0; base < rows && !rc; base += cnt, cur = std::min<uint64_t>(piece, 2ull * cur)) {
+    cnt = std::min<uint32_t>(cur, rows - base);
     Slot *s = nullptr;
     while (!s) {
       s = try_acquire(q, &rc);

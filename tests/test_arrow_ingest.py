@@ -198,3 +198,21 @@ def test_edge_cases_and_errors(A):
             A.arrow.scan_record_batch(q.h, bad2, _lib=A.lib)
         wrong_width = batch_of([b"\x01" * 32] * 5, [[1]] * 5, pa.binary(32))
         assert A.arrow.scan_record_batch(q.h, wrong_width, _lib=A.lib).tolist() == []
+
+
+def test_first_pieces_ramp_up(A):
+    """A scan starts with small pieces (1/8, 1/4, 1/2 of a full one) so that the device starts early."""
+    n = 300000
+    keys = np.zeros((n, 64), np.uint8)
+    keys[:, 1:9] = np.arange(n, dtype=np.int64).view(np.uint8).reshape(n, 8)
+    k = pa.FixedSizeBinaryArray.from_buffers(pa.binary(64), n, [None, pa.py_buffer(keys.tobytes())])
+    vals = np.arange(n, dtype=np.int64)
+    vals[1::2] = -1                                              # every even row matches the double's rule
+    outs = pa.ListArray.from_arrays(pa.array(np.arange(n + 1, dtype=np.int32)), pa.array(vals))
+    b = pa.record_batch({"tweak_key": k, "outputs": outs})
+    with A.query(piece=65536, cap_rows=65536, cap_outputs=65536, slots=3) as q:
+        ids = A.arrow.scan_record_batch(q.h, b, _lib=A.lib)
+        st = q.stats()
+    assert np.array_equal(ids, np.arange(0, n, 2, dtype=np.uint64))
+    # 8192 + 16384 + 32768 + 65536 * 3 + 46040 = 300000 -> 7 pieces instead of ceil(300000 / 65536) = 5
+    assert st["submits"] == 7 and st["rows"] == n
