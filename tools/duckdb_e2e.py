@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--labels", type=int, default=1)
     ap.add_argument("--threads", type=int, default=0)
     ap.add_argument("--batch", type=int, default=300000)
+    ap.add_argument("--compressed", action="store_true", help="store tweak_key as 33-byte SEC1 (decompressed on the GPU)")
+    ap.add_argument("--details", action="store_true", help="details := true (one result row per found output)")
     ap.add_argument("--in-memory", action="store_true", help="load the table into a DuckDB table first (no Parquet decode in the timed query)")
     a = ap.parse_args()
     import numpy as np
@@ -39,7 +41,11 @@ def main():
     T = synth.make_table(a.rows, 352003, n_labels=a.labels, n_base=100, n_per_label=100 if a.labels else 0, batch_rows=a.batch)
     rows = a.rows
     off = T["offsets"].astype(np.int64)
-    tw = pa.FixedSizeBinaryArray.from_buffers(pa.binary(64), rows, [None, pa.py_buffer(T["tweaks"].tobytes())]).cast(pa.binary())
+    if a.compressed:
+        from tests.test_gpu_compressed import compress
+        tw = pa.FixedSizeBinaryArray.from_buffers(pa.binary(33), rows, [None, pa.py_buffer(compress(T["tweaks"]).tobytes())]).cast(pa.binary())
+    else:
+        tw = pa.FixedSizeBinaryArray.from_buffers(pa.binary(64), rows, [None, pa.py_buffer(T["tweaks"].tobytes())]).cast(pa.binary())
     txid = np.zeros((rows, 32), np.uint8)
     txid[:, :8] = np.arange(rows, dtype=np.uint64).view(np.uint8).reshape(rows, 8)
     tx = pa.FixedSizeBinaryArray.from_buffers(pa.binary(32), rows, [None, pa.py_buffer(txid.tobytes())]).cast(pa.binary())
@@ -55,8 +61,8 @@ def main():
     if a.in_memory:
         pre += "CREATE TABLE t AS SELECT * FROM %s;\n" % src
         src = "t"
-    scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM %s), %s, %s, %s, batch_size := %d);" % (
-        src, blob(T["sk"]), blob(T["spend"]), labels, a.batch)
+    scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM %s), %s, %s, %s, batch_size := %d%s);" % (
+        src, blob(T["sk"]), blob(T["spend"]), labels, a.batch, ", details := true" if a.details else "")
     plain = "SELECT count(*), sum(height), sum(octet_length(tweak_key)), sum(len(outputs)) FROM %s;" % src
     sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + "SELECT current_setting('threads');\n"
     p = subprocess.run([DUCKDB, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
@@ -67,7 +73,7 @@ def main():
     vals = [l for l in lines if not l.startswith("Run Time")]
     want = len(T["expected"])
     ok = p.returncode == 0 and len(vals) >= 2 and int(vals[0]) == want and int(vals[1]) == want
-    res = {"rows": rows, "labels": a.labels, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
+    res = {"rows": rows, "labels": a.labels, "compressed": a.compressed, "details": a.details, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
            "matches_ok": ok, "scan_s_cold": times[0] if times else None, "scan_s_warm": times[1] if len(times) > 1 else None,
            "plain_read_s": times[2] if len(times) > 2 else None, "gen_s": round(gen_s, 1),
            "rows_per_s_warm": rows / times[1] if len(times) > 1 else None, "stderr": p.stderr[-300:]}
