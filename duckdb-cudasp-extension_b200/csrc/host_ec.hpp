@@ -4,6 +4,9 @@
 // kernels run (portable path), with complete (checked) addition.  No row data ever goes through
 // these functions; they are not a CPU fallback for the scan.
 #pragma once
+#include <algorithm>
+#include <thread>
+#include <atomic>
 #include <stdint.h>
 #include <string.h>
 #include <vector>
@@ -142,24 +145,31 @@ inline Big gtab_offset(int w) {
   for (int i = 0; i < 32; i++) le[i] = h[31 - i];
   return mod(Big::from_le(le, 32), N_ORDER());
 }
-// table[w * entries + d] = (d * 2^(wbits*w) + r_w) * G ; returns also sum_w r_w mod n
+// table[w * entries + d] = (d * 2^(wbits*w) + r_w) * G ; returns also sum_w r_w mod n.
+// The windows are independent once their base points 2^(wbits*w)*G are known, so they are filled by a few host threads
+// (the build is part of a process's first query: 0.25 s single-threaded for 20 x 8192 entries).
 inline void build_gtab(std::vector<ge> &table, Big &offset_sum, int wbits, int nwin) {
   const int entries = 1 << wbits;
   table.resize((size_t)nwin * entries);
   const Big n = N_ORDER();
-  HPoint base = generator();   // 2^(wbits*w) * G
   offset_sum = Big();
-  std::vector<gej> jac((size_t)entries);
-  std::vector<fe> pre((size_t)entries);
+  std::vector<HPoint> bases((size_t)nwin), firsts((size_t)nwin);
+  HPoint base = generator();   // 2^(wbits*w) * G
   for (int w = 0; w < nwin; w++) {
     Big rw = gtab_offset(w);
     offset_sum = mod(add(offset_sum, rw), n);
-    HPoint first = h_mul(rw, generator());
+    firsts[w] = h_mul(rw, generator());
+    bases[w] = base;
+    for (int b = 0; b < wbits; b++) base = h_dbl(base);
+  }
+  auto fill = [&](int w) {
+    std::vector<gej> jac((size_t)entries);
+    std::vector<fe> pre((size_t)entries);
     // Jacobian running sum cur += base, then ONE inversion for the whole window (Montgomery's trick).
     // The offsets make every partial sum a pseudo-random multiple of G: +-base or infinity cannot occur
-    // (checked below through Z != 0, which the incomplete addition would produce on a collision).
-    jac[0].x = first.x; jac[0].y = first.y; fe_set_u32(jac[0].z, 1);
-    for (int d = 1; d < entries; d++) gej_add_ge(jac[d], jac[d - 1], base.x, base.y);
+    // (checked by the tests through Z != 0, which the incomplete addition would produce on a collision).
+    jac[0].x = firsts[w].x; jac[0].y = firsts[w].y; fe_set_u32(jac[0].z, 1);
+    for (int d = 1; d < entries; d++) gej_add_ge(jac[d], jac[d - 1], bases[w].x, bases[w].y);
     fe acc;
     fe_set_u32(acc, 1);
     for (int d = 0; d < entries; d++) { pre[d] = acc; fe_mul(acc, acc, jac[d].z); }
@@ -177,8 +187,18 @@ inline void build_gtab(std::vector<ge> &table, Big &offset_sum, int wbits, int n
       fe_normalize(e.x);
       fe_normalize(e.y);
     }
-    for (int b = 0; b < wbits; b++) base = h_dbl(base);
+  };
+  unsigned nt = std::thread::hardware_concurrency();
+  nt = std::max(1u, std::min({nt ? nt : 1u, 8u, (unsigned)nwin}));
+  if (nt == 1) {
+    for (int w = 0; w < nwin; w++) fill(w);
+    return;
   }
+  std::atomic<int> next{0};
+  std::vector<std::thread> pool;
+  for (unsigned t = 0; t < nt; t++)
+    pool.emplace_back([&] { for (int w = next++; w < nwin; w = next++) fill(w); });
+  for (std::thread &t : pool) t.join();
 }
 
 }  // namespace host

@@ -20,7 +20,7 @@ def build(force=False):
     for so, extra in ((SO, []), (SO_EMUL, ["-DCSP_FE_EMUL"])):
         if force or not os.path.exists(so) or os.path.getmtime(so) < newest:
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-I", CSRC,
-                                   "-Wno-unknown-pragmas"] + extra + ["-o", so, SRC])
+                                   "-Wno-unknown-pragmas", "-pthread"] + extra + ["-o", so, SRC])
     return SO
 
 
