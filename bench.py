@@ -30,7 +30,21 @@ import numpy as np  # noqa: E402
 
 W32_BASE, W32_PER_LABEL = 231526, 674          # IMAD32 lane-ops per row
 W32_LADDER = 2 * (666 * 73 + 795 * 45)         # stage A alone = 168786
-SEED = 352002
+SEED = 352002          # C2 352002 (L=0), C3 352003 (L=1), C4 352004 (L=8)
+REF_SAMPLE_ROWS = 1200000   # reference arm: rows per GPU and step (4 batches), a bounded sample of the workload
+
+
+def table_params(L):
+    """(seed, planted base matches, planted matches per label) of the BASELINE config with L labels."""
+    return {0: (352002, 100, 0), 1: (352003, 100, 100), 8: (352004, 100, 50)}.get(L, (SEED + L, 100, 50))
+
+
+def metric_name(L):
+    return "cudasp_scan rows/sec (%d label%s)" % (L, "" if L == 1 else "s")     # BASELINE.json: "cudasp_scan rows/sec (1 label)"
+
+
+def shape_name(rows):
+    return {1000000: "1-week", 9400000: "8-week", 32700000: "32-week"}.get(rows, "custom")
 
 
 def parse():
@@ -39,8 +53,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--rows", type=int, default=1000000)
-    ap.add_argument("--labels", type=int, default=0)
+    # default workload = BASELINE.json configs[2] (C3): the configuration the metric "rows/sec (1 label)" is quoted on
+    ap.add_argument("--rows", type=int, default=9400000)
+    ap.add_argument("--labels", type=int, default=1)
     ap.add_argument("--batch", type=int, default=300000)
     ap.add_argument("--streams", type=int, default=2)
     return ap.parse_args()
@@ -145,26 +160,29 @@ def reference_arm(args, config, cores, synth):
             use_gecc = torch.cuda.is_available() and torch.cuda.device_count() >= args.gpus
         except Exception:
             use_gecc = False
-    base = {"impl": "reference", "metric": "cudasp_scan rows/sec", "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps,
+    base = {"impl": "reference", "metric": metric_name(L), "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "data": "synthetic",
             "config": config}
     # CPU port, bounded sample (always reported)
     sample = cores * 6000
-    Tc = synth.make_table(max(sample, 4000), SEED, n_labels=L, n_base=20, n_per_label=2 if L else 0, batch_rows=args.batch)
+    seed, n_base, per_label = table_params(L)
+    Tc = synth.make_table(max(sample, 4000), seed, n_labels=L, n_base=20, n_per_label=2 if L else 0, batch_rows=args.batch)
     cpu_sample(Tc, min(sample, 1000), cores)
     cpu_rate, n, dt, flags = cpu_sample(Tc, sample, cores)
     assert np.array_equal(np.nonzero(flags)[0], Tc["expected"][Tc["expected"] < n]), "oracle disagrees with planted matches"
     cpu_port = {"value": cpu_rate, "unit": "rows/s", "cores": cores, "kind": "port",
                 "sample": "%d rows, oracle/cudasp_oracle.c, %d pthreads, %.1f s" % (n, cores, dt)}
     if use_gecc:
-        rows = args.rows * args.gpus            # weak scaling: rows_per_gpu on each of N GPUs
-        T = synth.make_table(rows, SEED, n_labels=L, n_base=100, n_per_label=50 if L else 0, batch_rows=args.batch)
+        per_gpu = min(args.rows, REF_SAMPLE_ROWS)   # bounded sample: the reference needs ~1.3 s per million rows
+        rows = per_gpu * args.gpus                  # weak scaling: the same sample on each of N GPUs
+        T = synth.make_table(rows, seed, n_labels=L, n_base=n_base, n_per_label=per_label, batch_rows=args.batch)
         value, ms = gecc_reference_run(T, rows, args.batch, args.gpus, args.steps, max(args.warmup, 1))
         base.update({"value": value, "ms_per_step": ms, "dtype": "u32",
                      "cpu_baseline": {"value": value, "unit": "rows/s", "cores": args.gpus, "kind": "reference",
                                       "sample": "the UNMODIFIED reference GPU pipeline (src/cudasp_gpu.cu + gECC, compiled for sm_100 into "
-                                                "oracle/_ref by oracle/Makefile) on %d B200, whole %d-row table per step, %d host thread(s); "
-                                                "the reference has no CPU implementation of this path" % (args.gpus, rows, args.gpus)},
+                                                "oracle/_ref by oracle/Makefile) on %d B200, a %d-row sample of the workload per step (%d per GPU, %d labels), "
+                                                "%d host thread(s); the reference has no CPU implementation of this path"
+                                                % (args.gpus, rows, per_gpu, L, args.gpus)},
                      "cpu_port": cpu_port,
                      "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
     else:
@@ -181,9 +199,12 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     L = args.labels
     w32 = W32_BASE + W32_PER_LABEL * L
-    workload = "%d-row synthetic tweak table (1-week shape), %d labels, batch_size=%d, per GPU" % (args.rows, L, args.batch)
-    config = {"workload": workload, "rows_per_gpu": args.rows, "labels": L, "batch_size": args.batch, "seed": SEED,
-              "l2": "flushed (256 MiB write) between timed steps", "planted_matches": 100 + 50 * L}
+    seed, n_base, per_label = table_params(L)
+    workload = "%d-row synthetic tweak table (%s shape), %d label key(s), planted matches, batch_size=%d, per GPU" % (
+        args.rows, shape_name(args.rows), L, args.batch)
+    config = {"workload": workload, "rows_per_gpu": args.rows, "labels": L, "batch_size": args.batch, "seed": seed,
+              "l2": "flushed (256 MiB write) between timed steps; inputs per step (%.0f MB) also exceed L2" % (args.rows * 84e-6),
+              "planted_matches": n_base + per_label * L}
     from tests import synth
 
     # ------------------------------------------------------------------ reference arm
@@ -214,7 +235,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = local_rank
     torch.cuda.set_device(dev)
-    T = synth.make_table(args.rows, SEED + rank, n_labels=L, n_base=100, n_per_label=50 if L else 0, batch_rows=args.batch)
+    T = synth.make_table(args.rows, seed + 1000 * rank, n_labels=L, n_base=n_base, n_per_label=per_label, batch_rows=args.batch)
     rows = args.rows
     q = M.Query(T["sk"], T["spend"], T["labels"], devices=[dev], batch_rows=args.batch,
                 max_outputs_per_batch=int(np.diff(T["offsets"][:: args.batch]).max(initial=0)) + 17 * args.batch)
@@ -278,8 +299,12 @@ def main():
 
     # e2e: public host API, host buffers, copies inside the timed region
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
-    piece = min(args.batch, sms * 4 * 128 * 2)      # piece_rows in csrc/cudasp_capi.cu: the call streams in pieces of 2 K1 waves
-    pieces = [min(piece, rows - b) for b in range(0, rows, piece)]
+    piece = min(args.batch, sms * 4 * 128 * 2)      # piece_rows in csrc/cudasp_capi.cu: the call streams in pieces of 2 K1 waves,
+    pieces, cur, b = [], min(piece, max(piece // 8, 8192)), 0     # the first ones ramping up from 1/8 (scan_batch_impl)
+    while b < rows:
+        pieces.append(min(cur, rows - b))
+        b += pieces[-1]
+        cur = min(piece, 2 * cur)
     h2d = rows * 64 + int(T["outputs"].shape[0]) * 8 + (rows + len(pieces)) * 4
     d2h = sum((1 + min(c, 1024)) * 4 for c in pieces)
     for _ in range(2):
@@ -329,7 +354,7 @@ def main():
                                       "B200, host buffers in / flags out, %.3f s" % (nref, dt), "flags_equal_planted": ok}
             except Exception as ex:   # the baseline is optional; the product line must still print
                 gecc = {"unavailable": repr(ex)[:200]}
-        line = {"metric": "cudasp_scan rows/sec", "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
+        line = {"metric": metric_name(L), "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u32", "data": "synthetic", "config": config, "clocks": clocks,
                 "e2e": {"value": e2e, "unit": "rows/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
