@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--labels", type=int, default=1)
     ap.add_argument("--threads", type=int, default=0)
     ap.add_argument("--batch", type=int, default=300000)
+    ap.add_argument("--replicate", type=int, default=1, help="scan the same Parquet file N times in one query (N x rows rows)")
+    ap.add_argument("--geom-p", type=float, default=0.5, help="outputs per row = 1 + min(Geom(p), 15|63); C5 uses 0.25")
     ap.add_argument("--compressed", action="store_true", help="store tweak_key as 33-byte SEC1 (decompressed on the GPU)")
     ap.add_argument("--details", action="store_true", help="details := true (one result row per found output)")
     ap.add_argument("--in-memory", action="store_true", help="load the table into a DuckDB table first (no Parquet decode in the timed query)")
@@ -38,7 +40,8 @@ def main():
     import pyarrow.parquet as pq
     from tests import synth
     t0 = time.perf_counter()
-    T = synth.make_table(a.rows, 352003, n_labels=a.labels, n_base=100, n_per_label=100 if a.labels else 0, batch_rows=a.batch)
+    T = synth.make_table(a.rows, 352003, n_labels=a.labels, n_base=100, n_per_label=100 if a.labels else 0, batch_rows=a.batch,
+                         geom_p=a.geom_p, max_extra=63 if a.geom_p < 0.5 else 15)
     rows = a.rows
     off = T["offsets"].astype(np.int64)
     if a.compressed:
@@ -56,7 +59,7 @@ def main():
     pq.write_table(tbl, path, row_group_size=122880, compression="NONE")
     gen_s = time.perf_counter() - t0
     labels = "[" + ", ".join(blob(l) for l in T["labels"]) + "]" + ("" if T["labels"] else "::BLOB[]")
-    src = "read_parquet('%s')" % path
+    src = "read_parquet('%s')" % path if a.replicate == 1 else "read_parquet([%s])" % ", ".join(["'%s'" % path] * a.replicate)
     pre = "PRAGMA threads=%d;\n" % a.threads if a.threads else ""
     if a.in_memory:
         pre += "CREATE TABLE t AS SELECT * FROM %s;\n" % src
@@ -71,9 +74,10 @@ def main():
     lines = [l for l in p.stdout.strip().splitlines() if l]
     times = [float(l.split("real")[1].split()[0]) for l in lines if l.startswith("Run Time")]
     vals = [l for l in lines if not l.startswith("Run Time")]
-    want = len(T["expected"])
+    want = len(T["expected"]) * a.replicate
+    rows = rows * a.replicate
     ok = p.returncode == 0 and len(vals) >= 2 and int(vals[0]) == want and int(vals[1]) == want
-    res = {"rows": rows, "labels": a.labels, "compressed": a.compressed, "details": a.details, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
+    res = {"rows": rows, "replicate": a.replicate, "geom_p": a.geom_p, "mean_outputs": float(len(T["outputs"])) / a.rows, "labels": a.labels, "compressed": a.compressed, "details": a.details, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
            "matches_ok": ok, "scan_s_cold": times[0] if times else None, "scan_s_warm": times[1] if len(times) > 1 else None,
            "plain_read_s": times[2] if len(times) > 2 else None, "gen_s": round(gen_s, 1),
            "rows_per_s_warm": rows / times[1] if len(times) > 1 else None, "stderr": p.stderr[-300:]}
