@@ -42,6 +42,7 @@ struct CudaspScanBindData : public TableFunctionData {
 	string label_keys;  // n_labels * 64 B, concatenated
 	uint32_t n_labels = 0;
 	idx_t batch_size = DEFAULT_BATCH;
+	bool emit_early = false;  // emit_early := true (extension): matches leave during Execute, not only in Final
 	bool details = false;  // details := true (extension): one result row per found output, + k, output_index, label_index, t_k
 };
 
@@ -87,6 +88,7 @@ struct CudaspScanLocalState : public LocalTableFunctionState {
 	bool finalized = false;
 	bool is_output_thread = false;
 	bool have_slot = false;
+	bool input_consumed = false;  // emit_early: the current input chunk is already staged (we are being re-called for output)
 	double accumulate_s = 0, first_input = 0;
 	uint64_t rows_seen = 0, batches = 0;
 	cudasp_slot slot;
@@ -179,6 +181,13 @@ static unique_ptr<FunctionData> CudaspScanBind(ClientContext &context, TableFunc
 		result->batch_size = (idx_t)v;
 	}
 
+	auto ee = input.named_parameters.find("emit_early");
+	if (ee != input.named_parameters.end()) {
+		if (ee->second.type().id() != LogicalTypeId::BOOLEAN) {
+			throw InvalidInputException("emit_early parameter must be a BOOLEAN");
+		}
+		result->emit_early = !ee->second.IsNull() && ee->second.GetValue<bool>();
+	}
 	auto dt = input.named_parameters.find("details");
 	if (dt != input.named_parameters.end()) {
 		if (dt->second.type().id() != LogicalTypeId::BOOLEAN) {
@@ -440,14 +449,49 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 	}
 }
 
-// Never emits during Execute (same protocol as the reference, :534-552); finished batches are collected
+// Copy up to STANDARD_VECTOR_SIZE collected result rows into `output` (under the output lock: other workers may be
+// appending).  Returns true when more rows are waiting.
+static bool EmitRows(CudaspScanState &state, DataChunk &output) {
+	std::lock_guard<std::mutex> guard(state.output_lock);
+	const idx_t remaining = state.output_txids.size() - state.output_position;
+	const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, remaining);
+	if (n > 0) {
+		auto txid_out = FlatVector::GetData<string_t>(output.data[0]);
+		auto height_out = FlatVector::GetData<int32_t>(output.data[1]);
+		auto tweak_out = FlatVector::GetData<string_t>(output.data[2]);
+		for (idx_t i = 0; i < n; i++) {
+			const idx_t src = state.output_position + i;
+			txid_out[i] = StringVector::AddStringOrBlob(output.data[0], state.output_txids[src]);
+			height_out[i] = state.output_heights[src];
+			tweak_out[i] = StringVector::AddStringOrBlob(output.data[2], state.output_tweak_keys[src]);
+		}
+		if (state.details) {
+			auto k_out = FlatVector::GetData<uint32_t>(output.data[3]);
+			auto oi_out = FlatVector::GetData<uint32_t>(output.data[4]);
+			auto li_out = FlatVector::GetData<int32_t>(output.data[5]);
+			auto t_out = FlatVector::GetData<string_t>(output.data[6]);
+			for (idx_t i = 0; i < n; i++) {
+				const cudasp_match_detail &d = state.output_details[state.output_position + i];
+				k_out[i] = d.k;
+				oi_out[i] = d.output_index;
+				li_out[i] = d.label_index;
+				t_out[i] = StringVector::AddStringOrBlob(output.data[6], const_char_ptr_cast(d.t_k), 32);
+			}
+		}
+		output.SetCardinality(n);
+		state.output_position += n;
+	}
+	return state.output_position < state.output_txids.size();
+}
+
+// By default never emits during Execute (same protocol as the reference, :534-552); finished batches are collected
 // opportunistically so that slots recycle while the scan is still feeding rows.
 static OperatorResultType CudaspScanFunction(ExecutionContext &context, TableFunctionInput &data_p, DataChunk &input,
                                              DataChunk &output) {
 	auto &bind = data_p.bind_data->Cast<CudaspScanBindData>();
 	auto &state = data_p.global_state->Cast<CudaspScanState>();
 	auto &local = data_p.local_state->Cast<CudaspScanLocalState>();
-	if (input.size() > 0) {
+	if (input.size() > 0 && !local.input_consumed) {
 		const double t0 = TraceOn() ? NowSec() : 0;
 		if (TraceOn() && local.rows_seen == 0) {
 			local.first_input = t0;
@@ -459,6 +503,15 @@ static OperatorResultType CudaspScanFunction(ExecutionContext &context, TableFun
 			local.rows_seen += input.size();
 		}
 	}
+	if (bind.emit_early) {
+		// extension: hand finished matches downstream now instead of in Final.  When a full
+		// vector went out and more is waiting, DuckDB calls again with the SAME input: it must not be staged twice.
+		if (EmitRows(state, output) && output.size() == STANDARD_VECTOR_SIZE) {
+			local.input_consumed = true;
+			return OperatorResultType::HAVE_MORE_OUTPUT;
+		}
+	}
+	local.input_consumed = false;
 	return OperatorResultType::NEED_MORE_INPUT;
 }
 
@@ -498,34 +551,7 @@ static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &cont
 		}
 	}
 
-	const idx_t remaining = state.output_txids.size() - state.output_position;
-	const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, remaining);
-	if (n > 0) {
-		auto txid_out = FlatVector::GetData<string_t>(output.data[0]);
-		auto height_out = FlatVector::GetData<int32_t>(output.data[1]);
-		auto tweak_out = FlatVector::GetData<string_t>(output.data[2]);
-		for (idx_t i = 0; i < n; i++) {
-			const idx_t src = state.output_position + i;
-			txid_out[i] = StringVector::AddStringOrBlob(output.data[0], state.output_txids[src]);
-			height_out[i] = state.output_heights[src];
-			tweak_out[i] = StringVector::AddStringOrBlob(output.data[2], state.output_tweak_keys[src]);
-		}
-		if (state.details) {
-			auto k_out = FlatVector::GetData<uint32_t>(output.data[3]);
-			auto oi_out = FlatVector::GetData<uint32_t>(output.data[4]);
-			auto li_out = FlatVector::GetData<int32_t>(output.data[5]);
-			auto t_out = FlatVector::GetData<string_t>(output.data[6]);
-			for (idx_t i = 0; i < n; i++) {
-				const cudasp_match_detail &d = state.output_details[state.output_position + i];
-				k_out[i] = d.k;
-				oi_out[i] = d.output_index;
-				li_out[i] = d.label_index;
-				t_out[i] = StringVector::AddStringOrBlob(output.data[6], const_char_ptr_cast(d.t_k), 32);
-			}
-		}
-		output.SetCardinality(n);
-		state.output_position += n;
-	}
+	EmitRows(state, output);
 	return state.output_position < state.output_txids.size() ? OperatorFinalizeResultType::HAVE_MORE_OUTPUT
 	                                                         : OperatorFinalizeResultType::FINISHED;
 }
@@ -539,6 +565,7 @@ static void LoadInternal(ExtensionLoader &loader) {
 	func.in_out_function_final = CudaspScanFinalFunction;
 	func.named_parameters["batch_size"] = LogicalType::INTEGER;
 	func.named_parameters["details"] = LogicalType::BOOLEAN;
+	func.named_parameters["emit_early"] = LogicalType::BOOLEAN;
 	loader.RegisterFunction(func);
 }
 

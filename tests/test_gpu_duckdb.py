@@ -183,3 +183,31 @@ def test_details_parameter_through_duckdb(tmp_path):
     # details := false is the default schema
     rc, lines, err = run_sql("SELECT count(*) FROM %s;" % call.replace("batch_size := 1000", "details := false"), threads=2)
     assert rc == 0 and int(lines[0]) == len(want), err
+
+
+@pytest.mark.parametrize("threads", [1, 8])
+def test_emit_early_returns_the_same_rows(tmp_path, threads):
+    """emit_early := true (extension): matches leave during Execute; the result set must not change.  Every row of the
+    table matches here, so full output vectors (HAVE_MORE_OUTPUT re-entry with the same input chunk) are exercised."""
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    rows = 30000
+    T = synth.make_table(rows, 2718, n_labels=1, n_base=rows, n_per_label=0, batch_rows=2048, specials=False)
+    assert len(T["expected"]) == rows
+    off = T["offsets"].astype(np.int64)
+    tbl = pa.table({"txid": pa.array([i.to_bytes(4, "little") * 8 for i in range(rows)], pa.binary()),
+                    "height": pa.array(np.arange(rows, dtype=np.int32)),
+                    "tweak_key": pa.array([T["tweaks"][i].tobytes() for i in range(rows)], pa.binary()),
+                    "outputs": pa.array([T["outputs"][off[i]:off[i + 1]].tolist() for i in range(rows)], pa.list_(pa.int64()))})
+    path = str(tmp_path / "e.parquet")
+    pq.write_table(tbl, path, row_group_size=4096)
+    q = dict(scan_sk=T["sk"].hex(), spend=T["spend"].hex(), labels=[l.hex() for l in T["labels"]], batch_size=2048)
+    call = scan_call("read_parquet('%s')" % path, q)
+    early = call.replace("batch_size := 2048", "batch_size := 2048, emit_early := true")
+    for c in (early, early.replace("emit_early := true", "emit_early := true, details := true")):
+        rc, lines, err = run_sql("SELECT count(*), count(DISTINCT height), min(height), max(height), sum(height) FROM %s;" % c, threads=threads)
+        assert rc == 0, err
+        assert [int(x) for x in lines[0].split(",")] == [rows, rows, 0, rows - 1, rows * (rows - 1) // 2]
+    # a LIMIT can now be satisfied before the scan has finished (no assertion on time, only on the answer)
+    rc, lines, err = run_sql("SELECT height FROM %s LIMIT 5;" % early, threads=threads)
+    assert rc == 0 and len(lines) == 5, err
