@@ -133,22 +133,54 @@ int fail(cudasp_query *q, int code, const std::string &msg) {
       return fail(q, CUDASP_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));               \
   } while (0)
 
-// ---- per-process, per-device fixed-base table
+// ---- per-process, per-device fixed-base table, built ON the device (k_build_gtab) from the host's per-window seeds.
+// start_device_gtab only enqueues (so that the devices of one query build concurrently); get_device_gtab waits.
+struct DevGTab {
+  ge *table = nullptr;
+  ge *seeds = nullptr;       // [2][GTAB_NWIN]: firsts, bases
+  uint32_t *bad = nullptr;   // exceptional additions met by the builder (must stay 0)
+  bool pending = false, ready = false;
+};
 std::mutex g_gtab_mu;
-std::vector<ge *> g_gtab_dev;   // indexed by device ordinal
+std::vector<DevGTab> g_gtab_dev;   // indexed by device ordinal
 
+int start_device_gtab_locked(cudasp_query *q, int device) {
+  if ((int)g_gtab_dev.size() <= device) g_gtab_dev.resize(device + 1);
+  DevGTab &t = g_gtab_dev[device];
+  if (t.ready || t.pending) return 0;
+  const host::GTabHost &g = host::gtab_host();
+  CU(q, cudaSetDevice(device));
+  CU(q, cudaMalloc(&t.table, GTAB_TOTAL * sizeof(ge)));
+  CU(q, cudaMalloc(&t.seeds, 2 * (size_t)GTAB_NWIN * sizeof(ge)));
+  CU(q, cudaMalloc(&t.bad, sizeof(uint32_t)));
+  CU(q, cudaMemcpy(t.seeds, g.seeds.firsts.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
+  CU(q, cudaMemcpy(t.seeds + GTAB_NWIN, g.seeds.bases.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
+  CU(q, cudaMemset(t.bad, 0, sizeof(uint32_t)));
+  const uint64_t threads = (uint64_t)(GTAB_NWIN - 1) * (GTAB_ENTRIES / GTAB_EPT) + GTAB_TOP_ENTRIES / GTAB_EPT;
+  k_build_gtab<<<(unsigned)((threads + 127) / 128), 128>>>(t.table, t.seeds, t.seeds + GTAB_NWIN, t.bad);
+  CU(q, cudaGetLastError());
+  t.pending = true;
+  return 0;
+}
+int start_device_gtab(cudasp_query *q, int device) {
+  std::lock_guard<std::mutex> lk(g_gtab_mu);
+  return start_device_gtab_locked(q, device);
+}
 int get_device_gtab(cudasp_query *q, int device, ge **out) {
   std::lock_guard<std::mutex> lk(g_gtab_mu);
-  if ((int)g_gtab_dev.size() <= device) g_gtab_dev.resize(device + 1, nullptr);
-  if (!g_gtab_dev[device]) {
-    const host::GTabHost &g = host::gtab_host();
-    ge *d = nullptr;
+  int rc = start_device_gtab_locked(q, device);
+  if (rc) return rc;
+  DevGTab &t = g_gtab_dev[device];
+  if (t.pending) {
+    uint32_t bad = 0;
     CU(q, cudaSetDevice(device));
-    CU(q, cudaMalloc(&d, g.table.size() * sizeof(ge)));
-    CU(q, cudaMemcpy(d, g.table.data(), g.table.size() * sizeof(ge), cudaMemcpyHostToDevice));
-    g_gtab_dev[device] = d;
+    CU(q, cudaMemcpy(&bad, t.bad, sizeof bad, cudaMemcpyDeviceToHost));   // default stream: waits for the builder
+    t.pending = false;
+    if (bad) return fail(q, CUDASP_ERR_STATE, "fixed-base table builder met an exceptional addition");
+    t.ready = true;
   }
-  *out = g_gtab_dev[device];
+  if (!t.ready) return fail(q, CUDASP_ERR_STATE, "fixed-base table is not available on this device");
+  *out = t.table;
   return 0;
 }
 
@@ -479,6 +511,10 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
   q->batch_rows = batch_rows;
   if (max_outputs_per_batch == 0) max_outputs_per_batch = 4ull * batch_rows;
   q->devs.resize(devs.size());
+  for (size_t i = 0; i < devs.size(); i++) {   // first query of the process: every device builds its table, concurrently
+    rc = start_device_gtab(nullptr, devs[i]);
+    if (rc) { cudasp_query_destroy(q); return rc; }
+  }
   for (size_t i = 0; i < devs.size(); i++) {
     DevCtx &dc = q->devs[i];
     dc.device = devs[i];
@@ -1097,6 +1133,20 @@ int cudasp_scan_candidates_fmt(cudasp_query *q, const uint8_t *tweak_keys, int k
 int cudasp_scan_intermediates(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows, uint8_t *S_le, uint8_t *t_be,
                               uint8_t *P0_le) {
   return scan_debug(q, tweak_keys, rows, nullptr, S_le, t_be, P0_le);
+}
+
+int cudasp_debug_gtab(int device, uint32_t window, uint32_t first_digit, uint32_t n, uint8_t *out) {
+  if (!out) return fail(nullptr, CUDASP_ERR_ARG, "NULL argument");
+  if (window >= (uint32_t)GTAB_NWIN ||
+      (uint64_t)first_digit + n > (uint64_t)(window == (uint32_t)GTAB_NWIN - 1 ? GTAB_TOP_ENTRIES : GTAB_ENTRIES))
+    return fail(nullptr, CUDASP_ERR_ARG, "window / digit out of range");
+  ge *tab = nullptr;
+  int rc = get_device_gtab(nullptr, device, &tab);
+  if (rc) return rc;
+  if (n == 0) return CUDASP_OK;
+  CU(nullptr, cudaSetDevice(device));
+  CU(nullptr, cudaMemcpy(out, tab + (size_t)window * GTAB_ENTRIES + first_digit, (size_t)n * sizeof(ge), cudaMemcpyDeviceToHost));
+  return CUDASP_OK;
 }
 
 int cudasp_test_field(int device, int op, const uint8_t *a, const uint8_t *b, uint8_t *out, uint32_t n) {

@@ -104,10 +104,29 @@ CSP_HD void fe_lin1(fe &r, const fe &a) {
   fe_fold_signed_top(r, c);
 }
 
-// ---- doubling, a = 0:  3M + 4S
-//   XX = X^2, YY = Y^2, YYYY = YY^2, T = X*YY, M = 3*XX,
-//   X3 = M^2 - 8T,  Y3 = M*(4T - X3) - 8*YYYY,  Z3 = 2*Y*Z
+// ---- doubling, a = 0.  Two formulas, selected at compile time (CSP_DBL_2M5S):
+//   3M + 4S:  XX = X^2, YY = Y^2, YYYY = YY^2, T = X*YY, M = 3*XX,
+//             X3 = M^2 - 8T,  Y3 = M*(4T - X3) - 8*YYYY,  Z3 = 2*Y*Z
+//   2M + 5S:  T is obtained as ((X + YY)^2 - XX - YYYY) / 2, trading one multiplication for a squaring and
+//             two more linear combinations (the shape of the reference's dbl-2009-l, gECC/scripts/ec_ops.py:351-370)
 CSP_HD void gej_dbl(gej &r, const gej &p) {
+#if defined(CSP_DBL_2M5S)
+  fe xx, yy, yyyy, t2, m, u;
+  fe_sqr(xx, p.x);
+  fe_sqr(yy, p.y);
+  fe_add(t2, p.x, yy);
+  fe_mul(u, p.y, p.z);
+  fe_lin1<2>(r.z, u);
+  fe_sqr(yyyy, yy);
+  fe_sqr(t2, t2);
+  fe_lin3<1, -1, -1>(t2, t2, xx, yyyy);   // 2*X*YY
+  fe_lin1<3>(m, xx);
+  fe_sqr(u, m);
+  fe_lin2<1, -4>(r.x, u, t2);
+  fe_lin2<2, -1>(u, t2, r.x);
+  fe_mul(u, m, u);
+  fe_lin2<1, -8>(r.y, u, yyyy);
+#else
   fe xx, yy, yyyy, t, m, u;
   fe_sqr(xx, p.x);
   fe_sqr(yy, p.y);
@@ -121,6 +140,7 @@ CSP_HD void gej_dbl(gej &r, const gej &p) {
   fe_lin2<4, -1>(u, t, r.x);
   fe_mul(u, m, u);
   fe_lin2<1, -8>(r.y, u, yyyy);
+#endif
 }
 
 // ---- mixed addition r = p + q (q affine), p != +-q, neither infinity:  8M + 3S

@@ -145,23 +145,40 @@ inline Big gtab_offset(int w) {
   for (int i = 0; i < 32; i++) le[i] = h[31 - i];
   return mod(Big::from_le(le, 32), N_ORDER());
 }
-// table[w * entries + d] = (d * 2^(wbits*w) + r_w) * G ; returns also sum_w r_w mod n.
-// The windows are independent once their base points 2^(wbits*w)*G are known, so they are filled by a few host threads
-// (the build is part of a process's first query: 0.25 s single-threaded for 20 x 8192 entries).
-inline void build_gtab(std::vector<ge> &table, Big &offset_sum, int wbits, int nwin) {
-  const int entries = 1 << wbits;
-  table.resize((size_t)nwin * entries);
+// The seeds of the table: per window w its first entry r_w*G and its step 2^(wbits*w)*G (both affine, canonical),
+// plus sum_w r_w mod n.  The product builds the table from these ON THE DEVICE (k_build_gtab, kernels.cuh); the host
+// builder below is kept for the CPU logic tests and as the independent check of the device-built table.
+struct GTabSeeds {
+  std::vector<ge> firsts, bases;
+  Big offset_sum;
+};
+inline void gtab_seeds(GTabSeeds &sd, int wbits, int nwin) {
   const Big n = N_ORDER();
-  offset_sum = Big();
-  std::vector<HPoint> bases((size_t)nwin), firsts((size_t)nwin);
+  sd.firsts.resize((size_t)nwin);
+  sd.bases.resize((size_t)nwin);
+  sd.offset_sum = Big();
   HPoint base = generator();   // 2^(wbits*w) * G
   for (int w = 0; w < nwin; w++) {
     Big rw = gtab_offset(w);
-    offset_sum = mod(add(offset_sum, rw), n);
-    firsts[w] = h_mul(rw, generator());
-    bases[w] = base;
+    sd.offset_sum = mod(add(sd.offset_sum, rw), n);
+    HPoint f = h_mul(rw, generator());
+    sd.firsts[w].x = f.x; sd.firsts[w].y = f.y;
+    sd.bases[w].x = base.x; sd.bases[w].y = base.y;
+    fe_normalize(sd.firsts[w].x); fe_normalize(sd.firsts[w].y);
+    fe_normalize(sd.bases[w].x); fe_normalize(sd.bases[w].y);
     for (int b = 0; b < wbits; b++) base = h_dbl(base);
   }
+}
+// table[w * entries + d] = (d * 2^(wbits*w) + r_w) * G ; returns also sum_w r_w mod n.
+// The windows are independent once their base points 2^(wbits*w)*G are known, so they are filled by a few host threads
+// (0.25 s single-threaded for 20 x 8192 entries).  HOST builder: tests only, see gtab_seeds.
+inline void build_gtab(std::vector<ge> &table, Big &offset_sum, int wbits, int nwin) {
+  const int entries = 1 << wbits;
+  table.resize((size_t)nwin * entries);
+  GTabSeeds sd;
+  gtab_seeds(sd, wbits, nwin);
+  offset_sum = sd.offset_sum;
+  const std::vector<ge> &firsts = sd.firsts, &bases = sd.bases;
   auto fill = [&](int w) {
     std::vector<gej> jac((size_t)entries);
     std::vector<fe> pre((size_t)entries);

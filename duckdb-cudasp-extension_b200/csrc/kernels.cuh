@@ -248,4 +248,21 @@ __global__ void __launch_bounds__(32) k_details(const fe *__restrict__ SX, const
   }
 }
 
+// ---------------------------------------------------------------- fixed-base table, built where it is used
+// Replaces the reference's 256 x 64 B __constant__ table of 2^i*G uploaded by Solver::initialize (gsv.h:1094-1122).
+// One thread per GTAB_EPT consecutive entries of one window (rowfn.cuh gtab_chunk); runs once per process per device.
+__global__ void __launch_bounds__(128) k_build_gtab(ge *__restrict__ table, const ge *__restrict__ firsts,
+                                                    const ge *__restrict__ bases, uint32_t *__restrict__ bad) {
+  const uint64_t gid = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+  const uint32_t chunks_per_window = GTAB_ENTRIES / GTAB_EPT;
+  const uint32_t w = (uint32_t)(gid / chunks_per_window);
+  if (w >= (uint32_t)GTAB_NWIN) return;
+  const uint32_t d0 = (uint32_t)(gid % chunks_per_window) * GTAB_EPT;
+  if (w == (uint32_t)GTAB_NWIN - 1 && d0 >= (uint32_t)GTAB_TOP_ENTRIES) return;   // the top window is short
+  ge f, b;
+  load_fe_ro(f.x, &firsts[w].x); load_fe_ro(f.y, &firsts[w].y);
+  load_fe_ro(b.x, &bases[w].x); load_fe_ro(b.y, &bases[w].y);
+  if (!gtab_chunk(table + (size_t)w * GTAB_ENTRIES + d0, f, b, d0)) atomicAdd(bad, 1u);
+}
+
 }  // namespace csp

@@ -15,7 +15,7 @@ namespace csp {
 namespace host {
 
 struct GTabHost {
-  std::vector<ge> table;   // [GTAB_NWIN][GTAB_ENTRIES]
+  GTabSeeds seeds;         // per window: r_w*G and 2^(wbits*w)*G -- what the device builder starts from
   Big offset_sum;          // sum of r_w mod n
   HPoint offset_point;     // offset_sum * G
 };
@@ -23,10 +23,18 @@ inline const GTabHost &gtab_host() {
   static GTabHost g;
   static std::once_flag once;
   std::call_once(once, [] {
-    build_gtab(g.table, g.offset_sum, GTAB_WBITS, GTAB_NWIN);
+    gtab_seeds(g.seeds, GTAB_WBITS, GTAB_NWIN);
+    g.offset_sum = g.seeds.offset_sum;
     g.offset_point = h_mul(g.offset_sum, generator());
   });
   return g;
+}
+// the whole table built on the HOST: CPU logic tests only (the product builds it on the device)
+inline const std::vector<ge> &gtab_host_table() {
+  static std::vector<ge> table;
+  static std::once_flag once;
+  std::call_once(once, [] { Big s; build_gtab(table, s, GTAB_WBITS, GTAB_NWIN); });
+  return table;
 }
 
 struct QueryPlan {

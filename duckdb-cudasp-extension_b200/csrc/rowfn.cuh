@@ -15,9 +15,19 @@
 namespace csp {
 
 static const int LADDER_MAX_OPS_DEV = 240;
-static const int GTAB_WBITS = 13;                                      // fixed-base window width
-static const int GTAB_NWIN = (256 + GTAB_WBITS - 1) / GTAB_WBITS;      // 20 windows -> 19 mixed additions per row
-static const int GTAB_ENTRIES = 1 << GTAB_WBITS;                       // 20 * 8192 * 64 B = 10 MB, L2-resident
+// Fixed-base window width.  Every bit of width trades HBM for mixed additions in K3: 13 bits = 20 windows, 10 MB
+// (L2-resident), 19 additions; 22 bits = 12 windows, 2.95 GB of the 180 GB HBM3e, 11 additions -- K3 0.647 -> 0.414 ms per
+// 300 K rows on B200 (profiles/r01k_window_width.jsonl).  The table is built on the device (kernels.cuh k_build_gtab,
+// 0.17 s once per process per device), entries are read once per addition with a one-ahead prefetch.
+#ifndef CSP_GTAB_WBITS
+#define CSP_GTAB_WBITS 22
+#endif
+static const int GTAB_WBITS = CSP_GTAB_WBITS;                          // fixed-base window width
+static const int GTAB_NWIN = (256 + GTAB_WBITS - 1) / GTAB_WBITS;      // windows; NWIN - 1 mixed additions per row
+static const int GTAB_ENTRIES = 1 << GTAB_WBITS;                       // entries per window (stride of the table)
+static const int GTAB_TOP_BITS = 256 - GTAB_WBITS * (GTAB_NWIN - 1);   // the last window only sees the scalar's top bits
+static const int GTAB_TOP_ENTRIES = 1 << GTAB_TOP_BITS;                // ... so only that many of its entries exist
+static const size_t GTAB_TOTAL = (size_t)(GTAB_NWIN - 1) * GTAB_ENTRIES + GTAB_TOP_ENTRIES;
 
 // digit w of the 256-bit scalar t (little-endian limbs): bits [w*WBITS, w*WBITS + WBITS)
 CSP_HD uint32_t gtab_digit(const fe &t, int w) {
@@ -224,6 +234,75 @@ CSP_HD void batch_inv_thread(fe *vals, fe *scratch, uint32_t n, uint32_t T, uint
     store_fe(vals + i, out);
     if (i == tid) break;
   }
+}
+
+// ---------------------------------------------------------------- fixed-base table builder (once per process per device)
+// Entries d0 .. d0+GTAB_EPT-1 of one window:  out[i] = (d0 + i) * base + first, affine and canonical, where
+// base = 2^(WBITS*w)*G and first = r_w*G come from the host (host_ec.hpp gtab_seeds).  d0*base by double-and-add,
+// then a chain of mixed additions and ONE Fermat inversion for the chunk (Montgomery's trick).  Returns false when
+// an incomplete addition met P = +-Q (cannot happen with the published offsets; the caller refuses to continue).
+static const int GTAB_EPT = 16;
+static_assert(GTAB_TOP_ENTRIES >= GTAB_EPT && GTAB_ENTRIES % GTAB_EPT == 0, "window shape vs builder chunk");
+CSP_HD bool gtab_chunk(ge *out, const ge &first, const ge &base, uint32_t d0) {
+  gej pts[GTAB_EPT];
+  fe h;
+  bool ok = true;
+  if (d0 == 0) {
+    pts[0].x = first.x; pts[0].y = first.y; fe_set_u32(pts[0].z, 1);
+  } else {
+    gej acc;
+    acc.x = base.x; acc.y = base.y; fe_set_u32(acc.z, 1);
+    int top = 31;
+    while (!((d0 >> top) & 1u)) top--;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (int b = top - 1; b >= 0; b--) {
+      gej_dbl(acc, acc);
+      if ((d0 >> b) & 1u) {
+        gej_add_ge(acc, acc, base.x, base.y, &h);
+        ok &= !fe_is_zero(h);
+      }
+    }
+    gej_add_ge(pts[0], acc, first.x, first.y, &h);
+    ok &= !fe_is_zero(h);
+  }
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  for (int i = 1; i < GTAB_EPT; i++) {
+    gej_add_ge(pts[i], pts[i - 1], base.x, base.y, &h);
+    ok &= !fe_is_zero(h);
+  }
+  fe pre[GTAB_EPT];
+  pre[0] = pts[0].z;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  for (int i = 1; i < GTAB_EPT; i++) fe_mul(pre[i], pre[i - 1], pts[i].z);
+  fe inv;
+  fe_inv(inv, pre[GTAB_EPT - 1]);
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  for (int i = GTAB_EPT - 1; i >= 0; i--) {
+    fe zi, zi2, zi3, x, y;
+    if (i) {
+      fe_mul(zi, inv, pre[i - 1]);
+      fe_mul(inv, inv, pts[i].z);
+    } else {
+      zi = inv;
+    }
+    fe_sqr(zi2, zi);
+    fe_mul(zi3, zi2, zi);
+    fe_mul(x, pts[i].x, zi2);
+    fe_mul(y, pts[i].y, zi3);
+    fe_normalize(x);
+    fe_normalize(y);
+    store_fe(&out[i].x, x);
+    store_fe(&out[i].y, y);
+  }
+  return ok;
 }
 
 // acc = t*G + B_spend from the offset window table (see the comment below); t is taken as a 256-bit integer, not reduced.

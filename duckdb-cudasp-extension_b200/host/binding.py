@@ -12,7 +12,8 @@ from typing import Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libcudasp_b200.so")
+# CUDASP_B200_LIB: a differently-built copy of the same library (tuning builds, tools/build_variants.sh)
+LIB_PATH = os.environ.get("CUDASP_B200_LIB") or os.path.join(os.path.dirname(_HERE), "libcudasp_b200.so")
 _lib = None
 
 OK, ERR_ARG, ERR_CUDA, ERR_STATE, ERR_KEY = 0, -1, -2, -3, -4
@@ -44,7 +45,7 @@ EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "c
            "cudasp_scan_device", "cudasp_profile_stages", "cudasp_scan_candidates", "cudasp_scan_intermediates", "cudasp_test_field",
            "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory",
            "cudasp_scan_batch_fmt", "cudasp_submit_slot_fmt", "cudasp_scan_candidates_fmt",
-           "cudasp_query_enable_details", "cudasp_result_details", "cudasp_scan_batch_details"]
+           "cudasp_query_enable_details", "cudasp_result_details", "cudasp_scan_batch_details", "cudasp_debug_gtab"]
 
 
 def lib():
@@ -78,6 +79,7 @@ def lib():
         L.cudasp_scan_batch_details.argtypes = [vp, vp, C.c_int, vp, vp, C.c_uint32, vp, u32p, C.POINTER(MatchDetail), C.c_uint32, u32p]
         L.cudasp_scan_intermediates.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
         L.cudasp_test_field.argtypes = [C.c_int, C.c_int, vp, vp, vp, C.c_uint32]
+        L.cudasp_debug_gtab.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, vp]
         L.cudasp_launch_count.argtypes = [vp]
         L.cudasp_launch_count.restype = C.c_uint64
         L.cudasp_query_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 5
@@ -229,6 +231,16 @@ def profile_stages(q: "Query", device: int, d_tweaks: int, d_outputs: int, d_off
     ms = (C.c_float * 7)()
     q._check(lib().cudasp_profile_stages(q._h, device, d_tweaks, d_outputs, d_offsets, rows, d_ids, d_count, ms))
     return dict(zip(STAGES, [float(x) for x in ms]))
+
+
+def debug_gtab(window: int, first_digit: int, n: int, device: int = 0):
+    """n entries of the device-built fixed-base table as (x, y) integer pairs (include/cudasp.h cudasp_debug_gtab)."""
+    out = np.zeros(64 * max(n, 1), np.uint8)
+    rc = lib().cudasp_debug_gtab(device, window, first_digit, n, _ptr(out))
+    if rc:
+        raise CudaspError(rc, (lib().cudasp_last_error(None) or b"").decode())
+    return [(int.from_bytes(out[64 * i:64 * i + 32].tobytes(), "little"), int.from_bytes(out[64 * i + 32:64 * i + 64].tobytes(), "little"))
+            for i in range(n)]
 
 
 def test_field(op: int, a: Sequence[int], b: Sequence[int], device: int = 0):

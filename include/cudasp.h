@@ -182,6 +182,11 @@ int cudasp_scan_intermediates(cudasp_query *q, const uint8_t *tweak_keys, uint32
                               uint8_t *S_le, uint8_t *t_be, uint8_t *P0_le);
 /* Field KATs on the device: op 0 mul, 1 sqr(a), 2 add, 3 sub, 4 inv(a), 5 normalize(a); n elements of 32 B LE. */
 int cudasp_test_field(int device, int op, const uint8_t *a, const uint8_t *b, uint8_t *out, uint32_t n);
+/* n entries of the device's fixed-base table, window `window`, digits first_digit .. first_digit+n-1, 64 B LE x||y each:
+ * entry (w, d) must be (d * 2^(bits*w) + r_w) * G (bits = cudasp_query_info's fixed_window_bits).  The table is built
+ * on the device once per process (it replaces the reference's host-uploaded 2^i*G table, gECC gsv.h:1094-1122); the
+ * first call builds it when no query has done so yet. */
+int cudasp_debug_gtab(int device, uint32_t window, uint32_t first_digit, uint32_t n, uint8_t *out);
 /* Counters: number of kernel launches issued by this query so far; ladder schedule shape. */
 uint64_t cudasp_launch_count(const cudasp_query *q);
 int cudasp_query_info(const cudasp_query *q, int *n_devices, int *ladder_dbl, int *ladder_add, int *fixed_window_bits,

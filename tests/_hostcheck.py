@@ -8,8 +8,14 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = os.path.join(ROOT, "tests", "hostcheck", "host_check.cpp")
-SO = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck.so")
-SO_EMUL = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck_emul.so")   # -DCSP_FE_EMUL: the device carry-chain code, emulated
+# HOSTCHECK_DEFS="-DCSP_DBL_2M5S -DCSP_GTAB_WBITS=16": check a tuning build of the row functions (see csrc/Makefile VARIANT_DEFS)
+EXTRA_DEFS = os.environ.get("HOSTCHECK_DEFS", "").split()
+# the CPU logic tests build the whole fixed-base table on the host: they use 13-bit windows (160 K entries) whatever
+# width the product is compiled with (the window code is parametric; the device-built table has its own GPU test)
+WBITS_DEF = [] if any("CSP_GTAB_WBITS" in d for d in EXTRA_DEFS) else ["-DCSP_GTAB_WBITS=13"]
+_SUFFIX = ("_" + "".join(c if c.isalnum() else "_" for c in "".join(EXTRA_DEFS))) if EXTRA_DEFS else ""
+SO = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck%s.so" % _SUFFIX)
+SO_EMUL = os.path.join(ROOT, "tests", "hostcheck", "libhostcheck_emul%s.so" % _SUFFIX)   # -DCSP_FE_EMUL: the device carry-chain code, emulated
 CSRC = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "csrc")
 _lib = None
 
@@ -20,7 +26,7 @@ def build(force=False):
     for so, extra in ((SO, []), (SO_EMUL, ["-DCSP_FE_EMUL"])):
         if force or not os.path.exists(so) or os.path.getmtime(so) < newest:
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", "-I", CSRC,
-                                   "-Wno-unknown-pragmas", "-pthread"] + extra + ["-o", so, SRC])
+                                   "-Wno-unknown-pragmas", "-pthread"] + extra + WBITS_DEF + EXTRA_DEFS + ["-o", so, SRC])
     return SO
 
 
@@ -109,6 +115,18 @@ def gtab_entry(w, d):
     out = np.zeros(64, np.uint8)
     lib.hc_gtab_entry(w, d, _p(out))
     return out.tobytes()
+
+
+GTAB_EPT = 16
+
+
+def gtab_chunk(w, d0):
+    """rowfn.cuh gtab_chunk (the device table builder's row function) run on the CPU -> list of 64-byte entries"""
+    lib = load()
+    out = np.zeros(64 * GTAB_EPT, np.uint8)
+    n = lib.hc_gtab_chunk(w, C.c_uint32(d0), _p(out))
+    assert n == GTAB_EPT, "gtab_chunk reported an exceptional addition"
+    return [out[64 * i:64 * i + 64].tobytes() for i in range(n)]
 
 
 def decompress(sec1: bytes):

@@ -137,7 +137,7 @@ int hc_scan_candidates(const uint8_t sk[32], const uint8_t spend[64], const uint
   for (uint32_t r = 0; r < rows; r++) {
     gej acc;
     fe sx, sy, t;
-    hash_fixedbase_row(acc, X[r], Y[r], Z[r], g.table.data(), q.fp, &sx, &sy, &t);
+    hash_fixedbase_row(acc, X[r], Y[r], Z[r], gtab_host_table().data(), q.fp, &sx, &sy, &t);
     if (S_le) { fe_to_le_bytes(S_le + 64 * (size_t)r, sx); fe_to_le_bytes(S_le + 64 * (size_t)r + 32, sy); }
     if (t_be) for (int l = 0; l < 8; l++) {
       uint32_t wv = t.v[7 - l];
@@ -177,7 +177,7 @@ int hc_details_row(const uint8_t sk[32], const uint8_t spend[64], const uint8_t 
   fe_from_le_bytes(sx, S_le);
   fe_from_le_bytes(sy, S_le + 32);
   uint32_t n = 0;
-  details_row(sx, sy.v[0] & 1u, outputs, 0u, n_out, q.labels.data(), L, g.table.data(), q.fp,
+  details_row(sx, sy.v[0] & 1u, outputs, 0u, n_out, q.labels.data(), L, gtab_host_table().data(), q.fp,
               [&](uint32_t k, uint32_t oi, int32_t li, const fe &t) {
                 if (n >= cap) return;
                 uint8_t *o = out + 44 * (size_t)n++;
@@ -196,8 +196,16 @@ int hc_tweak_in_range(const uint8_t t_le[32]) { fe t; fe_from_le_bytes(t, t_le);
 // gtab[w][d] as 64 B LE
 void hc_gtab_entry(int w, int d, uint8_t out[64]) {
   const GTabHost &g = gtab_host();
-  const ge &e = g.table[(size_t)w * GTAB_ENTRIES + d];
+  const ge &e = gtab_host_table()[(size_t)w * GTAB_ENTRIES + d];
   fe_to_le_bytes(out, e.x); fe_to_le_bytes(out + 32, e.y);
+}
+// the DEVICE builder's row function (rowfn.cuh gtab_chunk) on the CPU: GTAB_EPT entries from digit d0 of window w
+int hc_gtab_chunk(int w, uint32_t d0, uint8_t *out /* GTAB_EPT x 64 B */) {
+  const GTabHost &g = gtab_host();
+  ge tmp[GTAB_EPT];
+  bool ok = gtab_chunk(tmp, g.seeds.firsts[w], g.seeds.bases[w], d0);
+  for (int i = 0; i < GTAB_EPT; i++) { fe_to_le_bytes(out + 64 * i, tmp[i].x); fe_to_le_bytes(out + 64 * i + 32, tmp[i].y); }
+  return ok ? GTAB_EPT : -1;
 }
 void hc_gtab_offset(int w, uint8_t out[32]) { gtab_offset(w).to_le(out, 32); }
 // 33-byte SEC1 -> 64 B LE x||y; returns 1 when valid

@@ -114,6 +114,21 @@ def test_gtab_entries():
         assert R.parse_point(H.gtab_entry(w, d)) == want
 
 
+def test_gtab_chunk_builder_equals_host_table_and_oracle():
+    # the device builds the table with gtab_chunk (double-and-add to the chunk's first digit, a chain of mixed
+    # additions, one shared inversion); here the same function runs on the CPU
+    wbits, nwin = H.gtab_shape()
+    ept = H.GTAB_EPT
+    last = (1 << wbits) - ept
+    for w, d0 in [(0, 0), (0, ept), (1, 5 * ept), (nwin // 2, last), (nwin - 1, 0), (nwin - 1, last), (3, 1 << (wbits - 1))]:
+        got = H.gtab_chunk(w, d0)
+        for i, e in enumerate(got):
+            assert e == H.gtab_entry(w, d0 + i)
+        for i in (0, ept - 1):
+            want = R.pt_mul((((d0 + i) << (wbits * w)) + H.gtab_offset(w)) % N, R.G)
+            assert R.parse_point(got[i]) == want
+
+
 def test_gtab_digits_cover_the_scalar():
     wbits, nwin = H.gtab_shape()
     rng = random.Random(11)
