@@ -192,7 +192,25 @@ def reference_arm(args, config, cores, synth):
     return base
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line of the contract goes to the process's real stdout; everything else libraries print to fd 1
+    during the run (NCCL's version banner, for one) has been sent to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -218,7 +236,7 @@ def main():
             return
         cores = os.cpu_count() or 1
         line = reference_arm(args, config, cores, synth)
-        print(json.dumps(line), flush=True)
+        emit(line)
         return
 
     # ------------------------------------------------------------------ our arm (GPU)
@@ -369,7 +387,7 @@ def main():
                 "cpu_baseline": {"value": cpu_rate, "unit": "rows/s", "cores": cores, "kind": "port",
                                  "sample": "%d rows of the same table, oracle/cudasp_oracle.c, %d pthreads, %.1f s" % (cpu_n, cores, cpu_dt)},
                 "gecc_baseline": gecc}
-        print(json.dumps(line), flush=True)
+        emit(line)
     q.close()
     if dist:
         dist.destroy_process_group()

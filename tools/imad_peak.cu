@@ -104,6 +104,21 @@ __global__ void __launch_bounds__(256) k_bench(uint32_t *out, uint32_t seed, lon
         if ((i & 1) == 0)
           asm volatile("mad.lo.cc.u32 %0, %3, %4, %0;\n\tmadc.hi.cc.u32 %1, %4, %4, %1;\n\taddc.u32 %2, %2, 0;"
                        : "+r"(r[2 * i]), "+r"(r[2 * i + 1]), "+r"(r[2 * i + 2]) : "r"(a), "r"(b));
+      } else if (MODE == 11) {
+        // carry-IN only: one IADD3 produces the carry, the IMAD.WIDE.X consumes it and produces none
+        if ((i & 1) == 0)
+          asm volatile("add.cc.u32 %2, %2, %4;\n\tmadc.lo.cc.u32 %0, %3, %4, %0;\n\tmadc.hi.u32 %1, %3, %4, %1;"
+                       : "+r"(r[2 * i]), "+r"(r[2 * i + 1]), "+r"(r[2 * i + 2]) : "r"(a), "r"(b));
+      } else if (MODE == 12) {
+        // carry IN and OUT: IADD3 (carry out) -> IMAD.WIDE.X (in, out) -> IADD3.X (in)
+        if ((i & 1) == 0)
+          asm volatile("add.cc.u32 %2, %2, %5;\n\tmadc.lo.cc.u32 %0, %4, %5, %0;\n\tmadc.hi.cc.u32 %1, %4, %5, %1;\n\taddc.u32 %3, %3, 0;"
+                       : "+r"(r[2 * i]), "+r"(r[2 * i + 1]), "+r"(r[2 * i + 2]), "+r"(r[2 * i + 3]) : "r"(a), "r"(b));
+      } else if (MODE == 13) {
+        // reference for 11/12: the two IADD3 alone (add.cc + addc)
+        if ((i & 1) == 0)
+          asm volatile("add.cc.u32 %0, %0, %3;\n\taddc.u32 %1, %1, %2;"
+                       : "+r"(r[2 * i]), "+r"(r[2 * i + 1]) : "r"(a), "r"(b));
       } else if (MODE == 7) {
         unsigned long long acc = ((unsigned long long)r[2 * i + 1] << 32) | r[2 * i];
         asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(a), "r"(b));
@@ -173,7 +188,11 @@ int main() {
   if (run<7>("imad_wide_with_dfma_each", 2, sms, 4, &r, false)) return 1;       // counts the IMAD.WIDEs only
   if (run<8>("wide_carry_out_plus_addc", 1, sms, 4, &r, false)) return 1;       // CHAINS/2 per trip, 1 product each... counted x2 below
   if (run<9>("row4_carry_chain_x2", 1, sms, 4, &r, false)) return 1;            // 8 products per trip
-  if (run<10>("unfused_lo_hi", 1, sms, 4, &r, true)) return 1;
+  if (run<10>("unfused_lo_hi", 1, sms, 4, &r, false)) return 1;
+  // the next three execute CHAINS/2 groups per trip but count CHAINS: divide the figure by 2 for groups per clock
+  if (run<11>("addcc_then_wide_carry_in", 1, sms, 4, &r, false)) return 1;      // group = IADD3 + IMAD.WIDE.X(in)
+  if (run<12>("addcc_wide_in_out_addc", 1, sms, 4, &r, false)) return 1;        // group = IADD3 + IMAD.WIDE.X(in,out) + IADD3.X
+  if (run<13>("addcc_addc_pair", 1, sms, 4, &r, true)) return 1;                // group = IADD3 + IADD3.X
   printf("}\n");
   return 0;
 }
