@@ -69,6 +69,17 @@ struct CudaspScanState : public GlobalTableFunctionState {
 	std::atomic<uint64_t> next_tag {1};
 	std::mutex inflight_lock;
 	std::unordered_map<uint64_t, unique_ptr<InFlightBatch>> inflight;
+	vector<unique_ptr<InFlightBatch>> meta_pool;  // collected batches' host columns, recycled (their vectors keep capacity)
+	// The first batches of a query are cut short (1/8, 1/4, 1/2 of batch_size, one round of devices each) so that the
+	// GPUs start while the workers are still filling their first full batch; batch_size stays the maximum.
+	std::atomic<uint32_t> batches_started {0};
+	uint32_t n_devices = 1;
+	uint32_t batch_size = 300000;
+	// Every worker fills its own batch, so threads x batch / 2 rows are still on the host when the input ends and the
+	// GPUs process them as a tail.  With many workers per GPU the batches are therefore cut to
+	// batch_size * 2 * devices / threads rows, but not below one full wave of K1 (148 SMs x 4 blocks x 128 rows on B200):
+	// batches of different workers run side by side on their slots' streams.
+	uint32_t steady_limit = 300000;
 
 	// protocol state, as in the reference: nothing is emitted before every worker has finalized (:554-591)
 	std::atomic<uint64_t> currently_adding {0};
@@ -95,6 +106,7 @@ struct CudaspScanLocalState : public LocalTableFunctionState {
 	uint32_t rows = 0;
 	uint64_t n_outputs = 0;
 	uint32_t key_bytes = 64;   // key format of the batch being filled
+	uint32_t batch_limit = 0;  // rows after which the batch being filled is submitted (<= batch_size, see batches_started)
 	unique_ptr<InFlightBatch> meta;
 };
 
@@ -237,6 +249,13 @@ static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &contex
 		throw IOException("cudasp_scan: GPU initialisation failed: %s", msg ? msg : "unknown error");
 	}
 	state->details = bind.details;
+	state->n_devices = (uint32_t)n_dev;
+	state->batch_size = (uint32_t)bind.batch_size;
+	{
+		const uint64_t wave = 148ull * 4 * 128;
+		const uint64_t share = (uint64_t)bind.batch_size * 2 * (uint64_t)n_dev / threads;
+		state->steady_limit = (uint32_t)MinValue<uint64_t>(bind.batch_size, MaxValue<uint64_t>(wave, share));
+	}
 	if (bind.details && cudasp_query_enable_details(state->query, 0) != CUDASP_OK) {
 		ThrowGpu(*state, "cudasp_query_enable_details");
 	}
@@ -290,6 +309,11 @@ static void CollectResult(CudaspScanState &state, const cudasp_result &r) {
 	if (cudasp_release_result(state.query, &r) != CUDASP_OK) {
 		ThrowGpu(state, "cudasp_release_result");
 	}
+	meta->txid_bytes.clear();
+	meta->txid_end.clear();
+	meta->heights.clear();
+	std::lock_guard<std::mutex> guard(state.inflight_lock);
+	state.meta_pool.push_back(std::move(meta));
 }
 
 // Collect every batch that has already finished (block == false) or every batch in flight (block == true).
@@ -339,7 +363,21 @@ static void EnsureSlot(CudaspScanState &state, CudaspScanLocalState &local) {
 	local.rows = 0;
 	local.n_outputs = 0;
 	local.slot.out_offsets[0] = 0;
-	local.meta = make_uniq<InFlightBatch>();
+	{
+		std::lock_guard<std::mutex> guard(state.inflight_lock);
+		if (!state.meta_pool.empty()) {
+			local.meta = std::move(state.meta_pool.back());
+			state.meta_pool.pop_back();
+		}
+	}
+	if (!local.meta) {
+		local.meta = make_uniq<InFlightBatch>();
+	}
+	const uint32_t round = state.batches_started++ / state.n_devices;
+	local.batch_limit = MaxValue<uint32_t>(MinValue<uint32_t>(state.steady_limit, 16384u), state.steady_limit >> (round < 3 ? 3 - round : 0));
+	local.meta->txid_bytes.reserve((size_t)local.batch_limit * 32);
+	local.meta->txid_end.reserve(local.batch_limit);
+	local.meta->heights.reserve(local.batch_limit);
 	local.meta->tweak_keys = local.slot.tweak_keys;
 }
 
@@ -443,7 +481,7 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 		meta.txid_end.push_back((uint32_t)meta.txid_bytes.size());
 		meta.heights.push_back(heights[hi]);
 		local.rows = row + 1;
-		if (local.rows >= bind.batch_size || local.rows >= local.slot.cap_rows) {
+		if (local.rows >= local.batch_limit || local.rows >= local.slot.cap_rows) {
 			SubmitSlot(state, local);
 		}
 	}

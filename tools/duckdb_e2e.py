@@ -27,7 +27,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=4000000)
     ap.add_argument("--labels", type=int, default=1)
-    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--threads", type=str, default="0", help="PRAGMA threads; a comma list runs the queries once per value on the same file")
     ap.add_argument("--batch", type=int, default=300000)
     ap.add_argument("--replicate", type=int, default=1, help="scan the same Parquet file N times in one query (N x rows rows)")
     ap.add_argument("--geom-p", type=float, default=0.5, help="outputs per row = 1 + min(Geom(p), 15|63); C5 uses 0.25")
@@ -60,28 +60,30 @@ def main():
     gen_s = time.perf_counter() - t0
     labels = "[" + ", ".join(blob(l) for l in T["labels"]) + "]" + ("" if T["labels"] else "::BLOB[]")
     src = "read_parquet('%s')" % path if a.replicate == 1 else "read_parquet([%s])" % ", ".join(["'%s'" % path] * a.replicate)
-    pre = "PRAGMA threads=%d;\n" % a.threads if a.threads else ""
-    if a.in_memory:
-        pre += "CREATE TABLE t AS SELECT * FROM %s;\n" % src
-        src = "t"
-    scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM %s), %s, %s, %s, batch_size := %d%s);" % (
-        src, blob(T["sk"]), blob(T["spend"]), labels, a.batch, ", details := true" if a.details else "")
-    plain = "SELECT count(*), sum(height), sum(octet_length(tweak_key)), sum(len(outputs)) FROM %s;" % src
-    sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + "SELECT current_setting('threads');\n"
-    p = subprocess.run([DUCKDB, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
-    if os.environ.get("CUDASP_TRACE"):
-        sys.stderr.write(p.stderr)
-    lines = [l for l in p.stdout.strip().splitlines() if l]
-    times = [float(l.split("real")[1].split()[0]) for l in lines if l.startswith("Run Time")]
-    vals = [l for l in lines if not l.startswith("Run Time")]
-    want = len(T["expected"]) * a.replicate
-    rows = rows * a.replicate
-    ok = p.returncode == 0 and len(vals) >= 2 and int(vals[0]) == want and int(vals[1]) == want
-    res = {"rows": rows, "replicate": a.replicate, "geom_p": a.geom_p, "mean_outputs": float(len(T["outputs"])) / a.rows, "labels": a.labels, "compressed": a.compressed, "details": a.details, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
-           "matches_ok": ok, "scan_s_cold": times[0] if times else None, "scan_s_warm": times[1] if len(times) > 1 else None,
-           "plain_read_s": times[2] if len(times) > 2 else None, "gen_s": round(gen_s, 1),
-           "rows_per_s_warm": rows / times[1] if len(times) > 1 else None, "stderr": p.stderr[-300:]}
-    print(json.dumps(res))
+    for threads in [int(x) for x in a.threads.split(',')]:
+        pre = "PRAGMA threads=%d;\n" % threads if threads else ""
+        cur = src
+        if a.in_memory:
+            pre += "CREATE TABLE t AS SELECT * FROM %s;\n" % src
+            cur = "t"
+        scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM %s), %s, %s, %s, batch_size := %d%s);" % (
+            cur, blob(T["sk"]), blob(T["spend"]), labels, a.batch, ", details := true" if a.details else "")
+        plain = "SELECT count(*), sum(height), sum(octet_length(tweak_key)), sum(len(outputs)) FROM %s;" % cur
+        sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + "SELECT current_setting('threads');\n"
+        p = subprocess.run([DUCKDB, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
+        if os.environ.get("CUDASP_TRACE"):
+            sys.stderr.write(p.stderr)
+        lines = [l for l in p.stdout.strip().splitlines() if l]
+        times = [float(l.split("real")[1].split()[0]) for l in lines if l.startswith("Run Time")]
+        vals = [l for l in lines if not l.startswith("Run Time")]
+        want = len(T["expected"]) * a.replicate
+        rows = a.rows * a.replicate
+        ok = p.returncode == 0 and len(vals) >= 2 and int(vals[0]) == want and int(vals[1]) == want
+        res = {"rows": rows, "replicate": a.replicate, "geom_p": a.geom_p, "mean_outputs": float(len(T["outputs"])) / a.rows, "labels": a.labels, "compressed": a.compressed, "details": a.details, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
+               "matches_ok": ok, "scan_s_cold": times[0] if times else None, "scan_s_warm": times[1] if len(times) > 1 else None,
+               "plain_read_s": times[2] if len(times) > 2 else None, "gen_s": round(gen_s, 1),
+               "rows_per_s_warm": rows / times[1] if len(times) > 1 else None, "stderr": p.stderr[-300:]}
+        print(json.dumps(res))
     try:
         os.remove(path)
         os.rmdir(d)
