@@ -144,21 +144,30 @@ struct DevGTab {
 std::mutex g_gtab_mu;
 std::vector<DevGTab> g_gtab_dev;   // indexed by device ordinal
 
+static void drop_device_gtab(DevGTab &t) {   // after a failed build: leave nothing half-made behind
+  cudaFree(t.table); cudaFree(t.seeds); cudaFree(t.bad);
+  t = DevGTab();
+}
 int start_device_gtab_locked(cudasp_query *q, int device) {
   if ((int)g_gtab_dev.size() <= device) g_gtab_dev.resize(device + 1);
   DevGTab &t = g_gtab_dev[device];
   if (t.ready || t.pending) return 0;
   const host::GTabHost &g = host::gtab_host();
-  CU(q, cudaSetDevice(device));
-  CU(q, cudaMalloc(&t.table, GTAB_TOTAL * sizeof(ge)));
-  CU(q, cudaMalloc(&t.seeds, 2 * (size_t)GTAB_NWIN * sizeof(ge)));
-  CU(q, cudaMalloc(&t.bad, sizeof(uint32_t)));
-  CU(q, cudaMemcpy(t.seeds, g.seeds.firsts.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
-  CU(q, cudaMemcpy(t.seeds + GTAB_NWIN, g.seeds.bases.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
-  CU(q, cudaMemset(t.bad, 0, sizeof(uint32_t)));
-  const uint64_t threads = (uint64_t)(GTAB_NWIN - 1) * (GTAB_ENTRIES / GTAB_EPT) + GTAB_TOP_ENTRIES / GTAB_EPT;
-  k_build_gtab<<<(unsigned)((threads + 127) / 128), 128>>>(t.table, t.seeds, t.seeds + GTAB_NWIN, t.bad);
-  CU(q, cudaGetLastError());
+  auto body = [&]() -> int {
+    CU(q, cudaSetDevice(device));
+    CU(q, cudaMalloc(&t.table, GTAB_TOTAL * sizeof(ge)));
+    CU(q, cudaMalloc(&t.seeds, 2 * (size_t)GTAB_NWIN * sizeof(ge)));
+    CU(q, cudaMalloc(&t.bad, sizeof(uint32_t)));
+    CU(q, cudaMemcpy(t.seeds, g.seeds.firsts.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
+    CU(q, cudaMemcpy(t.seeds + GTAB_NWIN, g.seeds.bases.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
+    CU(q, cudaMemset(t.bad, 0, sizeof(uint32_t)));
+    const uint64_t threads = (uint64_t)(GTAB_NWIN - 1) * (GTAB_ENTRIES / GTAB_EPT) + GTAB_TOP_ENTRIES / GTAB_EPT;
+    k_build_gtab<<<(unsigned)((threads + 127) / 128), 128>>>(t.table, t.seeds, t.seeds + GTAB_NWIN, t.bad);
+    CU(q, cudaGetLastError());
+    return 0;
+  };
+  const int rc = body();
+  if (rc) { drop_device_gtab(t); return rc; }
   t.pending = true;
   return 0;
 }
@@ -173,11 +182,17 @@ int get_device_gtab(cudasp_query *q, int device, ge **out) {
   DevGTab &t = g_gtab_dev[device];
   if (t.pending) {
     uint32_t bad = 0;
-    CU(q, cudaSetDevice(device));
-    CU(q, cudaMemcpy(&bad, t.bad, sizeof bad, cudaMemcpyDeviceToHost));   // default stream: waits for the builder
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaMemcpy(&bad, t.bad, sizeof bad, cudaMemcpyDeviceToHost);   // default stream: waits for the builder
+    if (e != cudaSuccess || bad) {
+      drop_device_gtab(t);
+      return e != cudaSuccess ? fail(q, CUDASP_ERR_CUDA, std::string("fixed-base table build: ") + cudaGetErrorString(e))
+                              : fail(q, CUDASP_ERR_STATE, "fixed-base table builder met an exceptional addition");
+    }
     t.pending = false;
-    if (bad) return fail(q, CUDASP_ERR_STATE, "fixed-base table builder met an exceptional addition");
     t.ready = true;
+    cudaFree(t.seeds); cudaFree(t.bad);
+    t.seeds = nullptr; t.bad = nullptr;
   }
   if (!t.ready) return fail(q, CUDASP_ERR_STATE, "fixed-base table is not available on this device");
   *out = t.table;

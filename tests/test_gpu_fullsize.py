@@ -1,7 +1,7 @@
 """GPU (-m gpu): BASELINE.json's configurations at FULL size through the C ABI, checked by properties that do not depend
 on the size (SURVEY.md 8c "oracle plan" iii): the match set equals the planted set, sampled rows' candidates equal the
 C oracle's, the result does not depend on how the table is cut into batches, a permuted table gives the permuted
-result, and a second scan gives the same answer.  C2 = 1 M rows, no labels, batch_size 300000; C3 = 9.4 M rows, 1 label."""
+result, and a second scan gives the same answer.  C2 = 1 M rows, no labels, batch_size 300000; C3 = 9.4 M rows, 1 label; C4 = 32.7 M rows, 8 labels."""
 import numpy as np
 import pytest
 
@@ -65,3 +65,13 @@ def test_c3_full_table_one_label(M):
         ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
         assert np.array_equal(ids, T["expected"])
         sampled_candidates_equal_oracle(M, q, T, n=2048, seed=3)
+
+
+def test_c4_full_table_eight_labels(M):
+    rows = 32700000
+    T = synth.make_table(rows, 352004, n_labels=8, n_base=100, n_per_label=50, batch_rows=300000, specials=True)
+    assert len(T["expected"]) >= 100 + 8 * 50
+    with M.Query(T["sk"], T["spend"], T["labels"], devices=[0], batch_rows=300000) as q:
+        ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
+        assert np.array_equal(ids, T["expected"])
+        sampled_candidates_equal_oracle(M, q, T, n=1024, seed=4)
