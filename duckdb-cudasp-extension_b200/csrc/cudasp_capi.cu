@@ -354,9 +354,11 @@ void launch_ladder(int variant, int keyfmt, const uint8_t *d_tweaks, fe *X, fe *
   switch (variant) {
     default:
     case 0: launch_ladder_t<128, 4, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;   // best measured (profiles/r01c)
+#if defined(CSP_LADDER_TUNING)   // the other shapes cost 25 s of ptxas each: only in tuning builds (VARIANT_DEFS=-DCSP_LADDER_TUNING)
     case 1: launch_ladder_t<128, 3, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
     case 2: launch_ladder_t<128, 4, 0, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
     case 3: launch_ladder_t<256, 2, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
+#endif
   }
 }
 

@@ -22,17 +22,19 @@ def main():
     t2 = time.perf_counter()
     T = synth.make_table(20000, 1, n_labels=0, n_base=5, batch_rows=300000, specials=False)
     t2b = time.perf_counter()
-    M.debug_gtab(0, 0, 1)                    # forces the device-side build of the fixed-base table (+ CUDA context)
+    all_devices = len(sys.argv) > 1 and sys.argv[1] == "--all-devices"     # one handle over every visible GPU
+    if not all_devices:
+        M.debug_gtab(0, 0, 1)                # forces the device-side build of the fixed-base table (+ CUDA context)
     t3 = time.perf_counter()
     gtab_s = t3 - t2b
-    q = M.Query(T["sk"], T["spend"], [], devices=[0], batch_rows=300000)
+    q = M.Query(T["sk"], T["spend"], [], devices=list(range(n)) if all_devices else [0], batch_rows=300000)
     t4 = time.perf_counter()
     ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
     t5 = time.perf_counter()
     ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
     t6 = time.perf_counter()
     q.close()
-    q2 = M.Query(T["sk"], T["spend"], [], devices=[0], batch_rows=300000)
+    q2 = M.Query(T["sk"], T["spend"], [], devices=list(range(n)) if all_devices else [0], batch_rows=300000)
     t7 = time.perf_counter()
     q2.close()
     print(json.dumps({"devices_visible": n, "load_lib_s": t1 - t0, "device_count_s": t2 - t1, "context_and_fixed_base_table_s": gtab_s, "first_query_create_s": t4 - t3,

@@ -3,6 +3,9 @@
 (CUDASP_LADDER_VARIANT, see csrc/cudasp_capi.cu launch_ladder) and check the match set each time.
 
     python tools/ladder_variants.py [variants...]        (GPU box)
+
+Variants 1-3 exist only in a library built with VARIANT_DEFS=-DCSP_LADDER_TUNING (csrc/Makefile); the production
+build has variant 0 alone and maps every other number to it.
 """
 import json
 import os
