@@ -33,6 +33,9 @@ __global__ void __launch_bounds__(256) k_bench(uint32_t *out, uint32_t seed, lon
 #pragma unroll
   for (int i = 0; i < CHAINS; i++) d[i] = (double)(a + i);
   double da = (double)a * 1e-9, db = (double)b * 1e-9;
+  uint32_t mm[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) mm[i] = a * (2 * i + 3) + b;
   long long t0 = clock64();
   for (int it = 0; it < ITERS; it++) {
 #pragma unroll
@@ -119,6 +122,13 @@ __global__ void __launch_bounds__(256) k_bench(uint32_t *out, uint32_t seed, lon
         if ((i & 1) == 0)
           asm volatile("add.cc.u32 %0, %0, %3;\n\taddc.u32 %1, %1, %2;"
                        : "+r"(r[2 * i]), "+r"(r[2 * i + 1]) : "r"(a), "r"(b));
+      } else if (MODE == 14) {
+        // plain IMAD.WIDE again, but every instruction reads DIFFERENT multiplier registers (no operand-reuse cache
+        // hits, as in a real 8x8 or 9x9 limb product; mode 2 multiplies the same two registers over and over)
+        unsigned long long acc = ((unsigned long long)r[2 * i + 1] << 32) | r[2 * i];
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(mm[i]), "r"(mm[(i + 3) & 7]));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(mm[(i + 5) & 7]), "r"(mm[(i + 6) & 7]));
+        r[2 * i] = (uint32_t)acc; r[2 * i + 1] = (uint32_t)(acc >> 32);
       } else if (MODE == 7) {
         unsigned long long acc = ((unsigned long long)r[2 * i + 1] << 32) | r[2 * i];
         asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(a), "r"(b));
@@ -192,7 +202,8 @@ int main() {
   // the next three execute CHAINS/2 groups per trip but count CHAINS: divide the figure by 2 for groups per clock
   if (run<11>("addcc_then_wide_carry_in", 1, sms, 4, &r, false)) return 1;      // group = IADD3 + IMAD.WIDE.X(in)
   if (run<12>("addcc_wide_in_out_addc", 1, sms, 4, &r, false)) return 1;        // group = IADD3 + IMAD.WIDE.X(in,out) + IADD3.X
-  if (run<13>("addcc_addc_pair", 1, sms, 4, &r, true)) return 1;                // group = IADD3 + IADD3.X
+  if (run<13>("addcc_addc_pair", 1, sms, 4, &r, false)) return 1;               // group = IADD3 + IADD3.X
+  if (run<14>("imad_wide_distinct_operands", 2, sms, 4, &r, true)) return 1;
   printf("}\n");
   return 0;
 }
