@@ -171,7 +171,7 @@ inline void gtab_seeds(GTabSeeds &sd, int wbits, int nwin) {
 }
 // table[w * entries + d] = (d * 2^(wbits*w) + r_w) * G ; returns also sum_w r_w mod n.
 // The windows are independent once their base points 2^(wbits*w)*G are known, so they are filled by a few host threads
-// (0.25 s single-threaded for 20 x 8192 entries).  HOST builder: tests only, see gtab_seeds.
+// (0.25 s single-threaded for 20 windows of 13 bits, the shape the CPU tests use).  HOST builder: tests only, see gtab_seeds.
 inline void build_gtab(std::vector<ge> &table, Big &offset_sum, int wbits, int nwin) {
   const int entries = 1 << wbits;
   table.resize((size_t)nwin * entries);

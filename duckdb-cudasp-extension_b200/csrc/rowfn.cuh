@@ -346,8 +346,8 @@ CSP_HD void fixedbase_plus_spend(gej &acc, const fe &t, const ge *gtab, const Fi
 // ---------------------------------------------------------------- K3 body: hash, t*G, + B_spend
 // in : shared secret S as Jacobian (X, Y) plus Zinv from the batch inversion
 // out: P0 = t*G + B_spend as Jacobian.
-// t*G uses the offset fixed-window table gtab[w][d] = (d * 2^(13w) + r_w) * G (affine, 64 B per
-// entry, 20 x 8192 entries = 10 MB, L2-resident): 19 mixed additions, no zero digits, no doublings.  The
+// t*G uses the offset fixed-window table gtab[w][d] = (d * 2^(WBITS*w) + r_w) * G (affine, 64 B per entry; with
+// WBITS = 22: 12 windows, 2.95 GB in HBM): GTAB_NWIN - 1 = 11 mixed additions, no zero digits, no doublings.  The
 // constant (sum r_w)*G is removed by adding spend_adj = B_spend - (sum r_w)*G instead of B_spend.
 // sx, sy, t_out (optional) receive the affine shared secret and the hash for the intermediates API.
 CSP_HD void hash_fixedbase_row(gej &acc, const fe &X, const fe &Y, const fe &Zinv, const ge *gtab, const FinalParams &fp,
