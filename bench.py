@@ -12,7 +12,7 @@ data path).  A "step" is one pass of the whole table through the hot path.
          staging, async H2D, kernels, D2H of the match ids -- all inside the timed region
   roofline  integer-multiply bound: achieved IMAD32 lane-ops/s of the dominant kernel
          (k_ladder) = rows * 168786 / its CUDA-event time, against the IMAD32 peak measured by
-         tools/imad_peak on this box (fallback: profiles/r01k_imad_peak.json)
+         tools/imad_peak on this box (fallback: profiles/r01n_imad_peak.json)
   cpu_baseline  the oracle's C port of the reference algorithm on the host cores, bounded sample
 """
 import argparse
@@ -99,8 +99,8 @@ def measured_imad_peak():
         out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
         return float(json.loads(out)["imad_lo"]["lane_ops_per_s"]), "measured live by tools/imad_peak (mad.lo.u32)"
     except Exception:
-        with open(os.path.join(ROOT, "profiles", "r01k_imad_peak.json")) as f:
-            return float(json.load(f)["imad_lo"]["lane_ops_per_s"]), "profiles/r01k_imad_peak.json (tools/imad_peak, earlier call)"
+        with open(os.path.join(ROOT, "profiles", "r01n_imad_peak.json")) as f:
+            return float(json.load(f)["imad_lo"]["lane_ops_per_s"]), "profiles/r01n_imad_peak.json (tools/imad_peak, earlier call)"
 
 
 def cpu_sample(T, rows_sample, threads):

@@ -47,9 +47,11 @@ __global__ void __launch_bounds__(256) k_bench(uint32_t *out, uint32_t seed, lon
         asm volatile("mad.hi.u32 %0, %1, %2, %0;" : "+r"(r[i]) : "r"(a), "r"(r[i]));
         asm volatile("mad.hi.u32 %0, %1, %2, %0;" : "+r"(r[i + CHAINS]) : "r"(b), "r"(r[i + CHAINS]));
       } else if (MODE == 2) {
+        // the multiplier is the low word of the NEIGHBOURING chain's accumulator: with loop-invariant multipliers ptxas
+        // computes a*b once and turns the loop into 64-bit additions (that is what the r01 figures of this mode measured)
         unsigned long long acc = ((unsigned long long)r[2 * i + 1] << 32) | r[2 * i];
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(a), "r"(b));
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(b), "r"(a));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 2) & 15]), "r"(b));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 4) & 15]), "r"(a));
         r[2 * i] = (uint32_t)acc; r[2 * i + 1] = (uint32_t)(acc >> 32);
       } else if (MODE == 3) {
         // a 4-word carry chain of two products, as in one row of a 256-bit operand-scanning product
@@ -65,8 +67,8 @@ __global__ void __launch_bounds__(256) k_bench(uint32_t *out, uint32_t seed, lon
         asm volatile("add.u32 %0, %0, %1;" : "+r"(r[i + CHAINS]) : "r"(b));
       } else if (MODE == 6) {
         unsigned long long acc = ((unsigned long long)r[2 * i + 1] << 32) | r[2 * i];
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(a), "r"(b));
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(b), "r"(a));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 2) & 15]), "r"(b));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 4) & 15]), "r"(a));
         r[2 * i] = (uint32_t)acc; r[2 * i + 1] = (uint32_t)(acc >> 32);
         uint32_t x = (uint32_t)__double_as_longlong(d[i]);
         asm volatile("add.u32 %0, %0, %1;" : "+r"(x) : "r"(a));
@@ -126,13 +128,13 @@ __global__ void __launch_bounds__(256) k_bench(uint32_t *out, uint32_t seed, lon
         // plain IMAD.WIDE again, but every instruction reads DIFFERENT multiplier registers (no operand-reuse cache
         // hits, as in a real 8x8 or 9x9 limb product; mode 2 multiplies the same two registers over and over)
         unsigned long long acc = ((unsigned long long)r[2 * i + 1] << 32) | r[2 * i];
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(mm[i]), "r"(mm[(i + 3) & 7]));
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(mm[(i + 5) & 7]), "r"(mm[(i + 6) & 7]));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 2) & 15]), "r"(mm[(i + 3) & 7]));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 6) & 15]), "r"(mm[(i + 6) & 7]));
         r[2 * i] = (uint32_t)acc; r[2 * i + 1] = (uint32_t)(acc >> 32);
       } else if (MODE == 7) {
         unsigned long long acc = ((unsigned long long)r[2 * i + 1] << 32) | r[2 * i];
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(a), "r"(b));
-        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(b), "r"(a));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 2) & 15]), "r"(b));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc) : "r"(r[(2 * i + 4) & 15]), "r"(a));
         r[2 * i] = (uint32_t)acc; r[2 * i + 1] = (uint32_t)(acc >> 32);
         asm volatile("fma.rn.f64 %0, %1, %2, %0;" : "+d"(d[i]) : "d"(da), "d"(db));
         asm volatile("fma.rn.f64 %0, %2, %1, %0;" : "+d"(d[i]) : "d"(da), "d"(db));
