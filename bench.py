@@ -14,6 +14,7 @@ data path).  A "step" is one pass of the whole table through the hot path.
          (k_ladder) = rows * 168786 / its CUDA-event time, against the IMAD32 peak measured by
          tools/imad_peak on this box (fallback: profiles/r01n_imad_peak.json)
   cpu_baseline  the oracle's C port of the reference algorithm on the host cores, bounded sample
+  python_baseline  the reference's own CPU code for the path is a pure-Python verifier: oracle/ref_scan.py, 1 core, ~4 s
 """
 import argparse
 import json
@@ -358,6 +359,24 @@ def main():
             traffic = json.load(open(tp)).get("k_ladder_dram_bytes_per_launch")
         cores = os.cpu_count() or 1
         cpu_rate, cpu_n, cpu_dt, _ = cpu_sample(T, min(rows, cores * 6000), cores)
+        py_base = None
+        if world == 1:
+            # the reference's only CPU code for this path is its Python verifier (scripts/verify_bip352_test_vector.py);
+            # oracle/ref_scan.py restates it row by row -- 1 core, a few seconds
+            try:
+                from oracle import ref_scan as RS
+                sk_i, spend_p = RS.parse_scalar(T["sk"]), RS.parse_point(T["spend"])
+                labels_p = [RS.parse_point(l) for l in T["labels"]]
+                tw = T["tweaks"].reshape(-1, 64)
+                n_py, t0p = 0, time.perf_counter()
+                while n_py < 400 and time.perf_counter() - t0p < 4.0:
+                    RS.row_candidates(sk_i, RS.parse_point(tw[n_py].tobytes()), spend_p, labels_p)
+                    n_py += 1
+                dtp = time.perf_counter() - t0p
+                py_base = {"value": n_py / dtp, "unit": "rows/s", "cores": 1, "kind": "port",
+                           "sample": "%d rows of the same table, oracle/ref_scan.py (pure Python, as the reference's verifier scripts), %.1f s" % (n_py, dtp)}
+            except Exception as ex:
+                py_base = {"unavailable": repr(ex)[:200]}
         gecc = None
         if world == 1:
             try:
@@ -386,7 +405,7 @@ def main():
                              "hbm_gbs_per_gpu": (value / world) * (64 + 8 * float(T["outputs"].shape[0]) / rows + 4) / 1e9},
                 "cpu_baseline": {"value": cpu_rate, "unit": "rows/s", "cores": cores, "kind": "port",
                                  "sample": "%d rows of the same table, oracle/cudasp_oracle.c, %d pthreads, %.1f s" % (cpu_n, cores, cpu_dt)},
-                "gecc_baseline": gecc}
+                "python_baseline": py_base, "gecc_baseline": gecc}
         emit(line)
     q.close()
     if dist:
