@@ -259,7 +259,14 @@ void free_slot(Slot &s) {
 }
 
 uint32_t inv_threads(uint32_t n) {
-  uint32_t t = (n + INV_ROWS_PER_THREAD - 1) / INV_ROWS_PER_THREAD;
+  // elements per Fermat inversion: more of them means less work (270 multiplications per inversion) but a longer
+  // single-thread chain; CUDASP_INV_PER_THREAD is a tuning aid, read once
+  static const uint32_t per = [] {
+    const char *e = getenv("CUDASP_INV_PER_THREAD");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? (uint32_t)v : INV_ROWS_PER_THREAD;
+  }();
+  uint32_t t = (n + per - 1) / per;
   t = (t + 127u) / 128u * 128u;
   return std::max<uint32_t>(std::min<uint32_t>(t, n), 1u);
 }
