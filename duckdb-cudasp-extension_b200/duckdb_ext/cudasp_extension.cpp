@@ -230,17 +230,25 @@ static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &contex
 		throw IOException("cudasp_scan: no CUDA device available (%s)", cudasp_last_error(nullptr));
 	}
 	idx_t threads = MaxValue<idx_t>(1, NumericCast<idx_t>(TaskScheduler::GetScheduler(context).NumberOfThreads()));
+	// rows per GPU batch: batch_size, cut down when there are many workers per GPU (see steady_limit)
+	{
+		const uint64_t wave = 148ull * 4 * 128;
+		const uint64_t share = (uint64_t)bind.batch_size * 2 * (uint64_t)n_dev / threads;
+		state->steady_limit = (uint32_t)MinValue<uint64_t>(bind.batch_size, MaxValue<uint64_t>(wave, share));
+	}
 	// every worker can hold one slot while filling it; two more per device keep a copy and a batch in flight
 	uint32_t slots = (uint32_t)MinValue<idx_t>(64, (threads + n_dev - 1) / n_dev + 2);
 	// cap the pinned/device footprint for very large batch sizes (~200 B of staging per row and slot)
-	while (slots > 3 && (uint64_t)slots * bind.batch_size > 48000000ull) {
+	while (slots > 3 && (uint64_t)slots * state->steady_limit > 48000000ull) {
 		slots--;
 	}
 	const double t_create = NowSec();
+	// the slots are sized for the batches that will actually be submitted (steady_limit rows, room for 8 outputs per row
+	// on average before a batch is cut early): less pinned and device memory to allocate on a query's first batches
 	int rc = cudasp_query_create_ex(const_data_ptr_cast(bind.scan_private_key.data()),
 	                                const_data_ptr_cast(bind.spend_public_key.data()),
 	                                bind.n_labels ? const_data_ptr_cast(bind.label_keys.data()) : nullptr, bind.n_labels,
-	                                nullptr, 0, (uint32_t)bind.batch_size, 0, slots, &state->query);
+	                                nullptr, 0, state->steady_limit, 8ull * state->steady_limit, slots, &state->query);
 	if (rc != CUDASP_OK) {
 		const char *msg = cudasp_last_error(nullptr);
 		if (rc == CUDASP_ERR_KEY || rc == CUDASP_ERR_ARG) {
@@ -251,11 +259,6 @@ static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &contex
 	state->details = bind.details;
 	state->n_devices = (uint32_t)n_dev;
 	state->batch_size = (uint32_t)bind.batch_size;
-	{
-		const uint64_t wave = 148ull * 4 * 128;
-		const uint64_t share = (uint64_t)bind.batch_size * 2 * (uint64_t)n_dev / threads;
-		state->steady_limit = (uint32_t)MinValue<uint64_t>(bind.batch_size, MaxValue<uint64_t>(wave, share));
-	}
 	if (bind.details && cudasp_query_enable_details(state->query, 0) != CUDASP_OK) {
 		ThrowGpu(*state, "cudasp_query_enable_details");
 	}
