@@ -167,19 +167,30 @@ struct LadderPlan {
   int n_dbl, n_add;
 };
 
-inline LadderPlan make_ladder_plan(const uint8_t scan_sk_le[32]) {
+// signed helper for the decomposition search: a + sign*b on (magnitude, sign) pairs
+inline SignedScalar signed_add(const SignedScalar &a, const Big &bmag, bool bneg) {
+  SignedScalar r;
+  if (a.neg == bneg) { r.mag = add(a.mag, bmag); r.neg = a.neg; return r; }
+  if (cmp(a.mag, bmag) >= 0) { r.mag = sub(a.mag, bmag); r.neg = a.neg; }
+  else { r.mag = sub(bmag, a.mag); r.neg = bneg; }
+  if (r.mag.is_zero()) r.neg = false;
+  return r;
+}
+// lattice of pairs (a, b) with a + b*lambda = 0 (mod n): v1 = (A1, -MINUS_B1), v2 = (A2, B2), B2 = A1
+inline Big GLV_A2() { static const uint64_t v[3] = {0x1ULL, 0x14CA50F7A8E2F3F6ULL, 0x57C1108D9D44CFD8ULL}; return Big::from_words_be(v, 3); }
+
+// op list for k1 + k2*lambda with the halves given as signed magnitudes (interleaved width-4 NAFs, one doubling chain)
+inline LadderPlan ladder_plan_from_halves(const SignedScalar &k1, const SignedScalar &k2) {
   LadderPlan p;
   memset(&p, 0, sizeof p);
-  const Big n = N_ORDER();
-  Big k = mod(Big::from_le(scan_sk_le, 32), n);
-  if (k.is_zero()) { p.zero = true; return p; }
-  SignedScalar k1, k2;
-  glv_split(k, k1, k2);
   std::vector<int> d1 = wnaf(k1.mag, LADDER_W), d2 = wnaf(k2.mag, LADDER_W);
   int len = (int)(d1.size() > d2.size() ? d1.size() : d2.size());
   bool started = false;
   for (int i = len - 1; i >= 0; i--) {
-    if (started) { p.ops[p.nops++] = OP_DBL; p.n_dbl++; }
+    if (started) {
+      if (p.nops >= LADDER_MAX_OPS) { p.nops = LADDER_MAX_OPS + 1; return p; }
+      p.ops[p.nops++] = OP_DBL; p.n_dbl++;
+    }
     for (int which = 0; which < 2; which++) {
       const std::vector<int> &d = which ? d2 : d1;
       int di = i < (int)d.size() ? d[i] : 0;
@@ -188,11 +199,30 @@ inline LadderPlan make_ladder_plan(const uint8_t scan_sk_le[32]) {
       int idx = ((di < 0 ? -di : di) - 1) / 2;
       uint8_t op = (uint8_t)(idx | (which ? OP_LAMBDA : 0) | (neg ? OP_NEG : 0));
       if (!started) { op |= OP_SET; started = true; } else p.n_add++;
+      if (p.nops >= LADDER_MAX_OPS) { p.nops = LADDER_MAX_OPS + 1; return p; }
       p.ops[p.nops++] = op;
     }
   }
   return p;
 }
+// field multiplications K1 spends on a plan (3M + 4S per doubling, 8M + 3S per mixed addition)
+inline int ladder_plan_cost(const LadderPlan &p) { return 7 * p.n_dbl + 11 * p.n_add; }
+
+// variant (i, j), i, j in {-1, 0, 1}: the balanced split moved by i*v1 + j*v2 -- the same scalar mod n, other digits.
+// (0, 0) is the balanced split itself.
+inline LadderPlan make_ladder_plan_variant(const uint8_t scan_sk_le[32], int i, int j) {
+  LadderPlan p;
+  memset(&p, 0, sizeof p);
+  const Big n = N_ORDER();
+  Big k = mod(Big::from_le(scan_sk_le, 32), n);
+  if (k.is_zero()) { p.zero = true; return p; }
+  SignedScalar k1, k2;
+  glv_split(k, k1, k2);
+  if (i) { k1 = signed_add(k1, GLV_B2(), i < 0); k2 = signed_add(k2, GLV_MINUS_B1(), i > 0); }   // v1 = (A1, b1), A1 = B2, b1 < 0
+  if (j) { k1 = signed_add(k1, GLV_A2(), j < 0); k2 = signed_add(k2, GLV_B2(), j < 0); }          // v2 = (A2, B2)
+  return ladder_plan_from_halves(k1, k2);
+}
+inline LadderPlan make_ladder_plan(const uint8_t scan_sk_le[32]) { return make_ladder_plan_variant(scan_sk_le, 0, 0); }
 
 }  // namespace host
 }  // namespace csp

@@ -77,6 +77,27 @@ def plan(sk_le):
     return dict(ops=ops[:nops].tolist(), n_dbl=n_dbl, n_add=n_add, zero=bool(zero), regular=bool(regular))
 
 
+def plan_variant(sk_le, i, j):
+    lib = load()
+    ops = np.zeros(256, np.uint8)
+    v = [C.c_int() for _ in range(4)]
+    lib.hc_plan_variant(_p(_b(sk_le)), i, j, _p(ops), *[C.byref(x) for x in v])
+    nops, n_dbl, n_add, regular = [x.value for x in v]
+    if nops < 0:
+        return None
+    return dict(ops=ops[:nops].tolist(), n_dbl=n_dbl, n_add=n_add, regular=bool(regular))
+
+
+def plan_chosen(sk_le):
+    lib = load()
+    ops = np.zeros(256, np.uint8)
+    v = [C.c_int() for _ in range(3)]
+    rc = lib.hc_plan_chosen(_p(_b(sk_le)), _p(ops), *[C.byref(x) for x in v])
+    assert rc == 0
+    nops, n_dbl, n_add = [x.value for x in v]
+    return dict(ops=ops[:nops].tolist(), n_dbl=n_dbl, n_add=n_add)
+
+
 def midstate():
     lib = load()
     out = np.zeros(8, np.uint32)

@@ -80,6 +80,28 @@ int hc_plan(const uint8_t sk[32], uint8_t *ops, int *nops, int *n_dbl, int *n_ad
   return 0;
 }
 
+// the nine equivalent decompositions (scalar_host.hpp make_ladder_plan_variant) and the one make_query_plan picks
+int hc_plan_variant(const uint8_t sk[32], int i, int j, uint8_t *ops, int *nops, int *n_dbl, int *n_add, int *regular) {
+  LadderPlan p = make_ladder_plan_variant(sk, i, j);
+  if (p.zero || p.nops > LADDER_MAX_OPS) { *nops = -1; return 0; }
+  memcpy(ops, p.ops, (size_t)p.nops);
+  *nops = p.nops; *n_dbl = p.n_dbl; *n_add = p.n_add;
+  *regular = ladder_plan_is_regular(p) ? 1 : 0;
+  return 0;
+}
+int hc_plan_chosen(const uint8_t sk[32], uint8_t *ops, int *nops, int *n_dbl, int *n_add) {
+  QueryPlan q;
+  std::string err;
+  uint8_t spend[64];
+  HPoint g = generator();
+  fe_to_le_bytes(spend, g.x); fe_to_le_bytes(spend + 32, g.y);
+  int rc = make_query_plan(q, sk, spend, nullptr, 0, err);
+  if (rc) return rc;
+  memcpy(ops, q.lp.ops, (size_t)q.lp.nops);
+  *nops = q.lp.nops; *n_dbl = q.n_dbl; *n_add = q.n_add;
+  return 0;
+}
+
 void hc_midstate(uint32_t out[8]) { bip352_midstate(out); }
 
 // k * P for n points (64 B LE each) through ladder_row; out = affine 64 B LE

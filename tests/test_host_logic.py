@@ -90,6 +90,50 @@ def test_plan_shape_and_regularity():
     assert H.plan((0).to_bytes(32, "little"))["zero"] and H.plan(N.to_bytes(32, "little"))["zero"]
 
 
+LAMBDA = 0x5363AD4CC05C30E0A5261C028812645A122E22EA20816678DF02967C1B23BD72
+
+
+def plan_scalar(ops):
+    """the scalar (mod n) an op list makes the ladder compute: DBL doubles, ADD adds +-(2*idx+1) or that times lambda"""
+    v = 0
+    for o in ops:
+        if o & 0x80:
+            v = 2 * v % N
+            continue
+        d = 2 * (o & 3) + 1
+        if o & 0x04:
+            d = d * LAMBDA % N
+        if o & 0x08:
+            d = -d
+        v = (v + d) % N
+    return v
+
+
+def test_decomposition_variants_encode_the_same_scalar_and_the_cheapest_is_chosen():
+    rng = random.Random(9)
+    saved = total = 0
+    for k in [1, 2, 3, N - 1, N + 1, (1 << 256) - 1] + [rng.randrange(1, 1 << 256) for _ in range(60)]:
+        sk = k.to_bytes(32, "little")
+        costs = {}
+        for i in (-1, 0, 1):
+            for j in (-1, 0, 1):
+                p = H.plan_variant(sk, i, j)
+                if p is None:
+                    continue
+                assert plan_scalar(p["ops"]) == k % N, (k, i, j)
+                assert p["ops"][0] & 0x40 and not any(o & 0x40 for o in p["ops"][1:])
+                if p["regular"]:
+                    costs[(i, j)] = 7 * p["n_dbl"] + 11 * p["n_add"]
+        assert (0, 0) in costs
+        c = H.plan_chosen(sk)
+        assert plan_scalar(c["ops"]) == k % N
+        assert 7 * c["n_dbl"] + 11 * c["n_add"] == min(costs.values())
+        assert c["n_dbl"] <= 132 and c["n_add"] <= 60
+        saved += costs[(0, 0)] - min(costs.values())
+        total += costs[(0, 0)]
+    assert saved > 0.005 * total        # about 1.6 % on average
+
+
 @pytest.mark.parametrize("key", ["pmul_seed42", "pmul_gpu_dumps", "pmul_batch_seed42"])
 def test_ladder_kats(golden, key):
     for k in golden[key]:
