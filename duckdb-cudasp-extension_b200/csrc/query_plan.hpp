@@ -5,6 +5,7 @@
 // (src/cudasp_extension.cu:277-297,343-361) and per thread in CheckMatchesWithLabelsKernel
 // (spend key / labels to Montgomery form, src/cudasp_gpu.cu:109-116,154-161).
 #pragma once
+#include <algorithm>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -36,6 +37,8 @@ inline const std::vector<ge> &gtab_host_table() {
   std::call_once(once, [] { Big s; build_gtab(table, s, GTAB_WBITS, GTAB_NWIN); });
   return table;
 }
+
+static const int LADDER_SEARCH = 2;   // decomposition search radius (make_query_plan)
 
 struct QueryPlan {
   LadderParams lp;
@@ -77,19 +80,28 @@ inline int make_query_plan(QueryPlan &q, const uint8_t sk[32], const uint8_t spe
                            uint32_t n_labels, std::string &err) {
   memset(&q.lp, 0, sizeof q.lp);
   memset(&q.fp, 0, sizeof q.fp);
-  // The scan key is fixed for the whole query, so its recoding may be chosen at leisure: among the nine GLV
-  // decompositions k1 + i*a1 + j*a2, k2 + i*b1 + j*b2 (i, j in {-1, 0, 1}; all equal k mod n, all about 128 bits) take the
-  // one whose interleaved NAFs cost K1 the fewest field multiplications -- 1.6 % fewer on average than the balanced split.
+  // The scan key is fixed for the whole query, so its recoding may be chosen at leisure: among the 25 GLV
+  // decompositions k1 + i*a1 + j*a2, k2 + i*b1 + j*b2 (|i|, |j| <= 2; all equal k mod n, all about 128 bits) take the
+  // one whose interleaved NAFs cost K1 the fewest field multiplications -- 2 % fewer on average than the balanced split.
+  // Candidates are tried cheapest first; the regularity check (big-number arithmetic) runs until one passes.
   LadderPlan lp = make_ladder_plan(sk);
   if (!lp.zero) {
-    bool have = lp.nops <= LADDER_MAX_OPS_DEV && ladder_plan_is_regular(lp);
-    for (int i = -1; i <= 1; i++)
-      for (int j = -1; j <= 1; j++) {
-        if (!i && !j) continue;
-        LadderPlan c = make_ladder_plan_variant(sk, i, j);
-        if (c.nops > LADDER_MAX_OPS_DEV || !ladder_plan_is_regular(c)) continue;
-        if (!have || ladder_plan_cost(c) < ladder_plan_cost(lp)) { lp = c; have = true; }
+    struct Cand { int cost, i, j; };
+    std::vector<Cand> cands;
+    for (int i = -LADDER_SEARCH; i <= LADDER_SEARCH; i++)
+      for (int j = -LADDER_SEARCH; j <= LADDER_SEARCH; j++) {
+        LadderPlan c = (i || j) ? make_ladder_plan_variant(sk, i, j) : lp;
+        if (c.nops > LADDER_MAX_OPS_DEV) continue;
+        cands.push_back({ladder_plan_cost(c), i, j});
       }
+    std::stable_sort(cands.begin(), cands.end(), [](const Cand &a, const Cand &b) {
+      if (a.cost != b.cost) return a.cost < b.cost;
+      return (a.i * a.i + a.j * a.j) < (b.i * b.i + b.j * b.j);     // ties: the decomposition closest to the balanced one
+    });
+    for (const Cand &c : cands) {
+      LadderPlan p = (c.i || c.j) ? make_ladder_plan_variant(sk, c.i, c.j) : lp;
+      if (ladder_plan_is_regular(p)) { lp = p; break; }
+    }
   }
   q.n_dbl = lp.n_dbl;
   q.n_add = lp.n_add;

@@ -208,7 +208,7 @@ inline LadderPlan ladder_plan_from_halves(const SignedScalar &k1, const SignedSc
 // field multiplications K1 spends on a plan (3M + 4S per doubling, 8M + 3S per mixed addition)
 inline int ladder_plan_cost(const LadderPlan &p) { return 7 * p.n_dbl + 11 * p.n_add; }
 
-// variant (i, j), i, j in {-1, 0, 1}: the balanced split moved by i*v1 + j*v2 -- the same scalar mod n, other digits.
+// variant (i, j), small integers: the balanced split moved by i*v1 + j*v2 -- the same scalar mod n, other digits.
 // (0, 0) is the balanced split itself.
 inline LadderPlan make_ladder_plan_variant(const uint8_t scan_sk_le[32], int i, int j) {
   LadderPlan p;
@@ -218,8 +218,8 @@ inline LadderPlan make_ladder_plan_variant(const uint8_t scan_sk_le[32], int i, 
   if (k.is_zero()) { p.zero = true; return p; }
   SignedScalar k1, k2;
   glv_split(k, k1, k2);
-  if (i) { k1 = signed_add(k1, GLV_B2(), i < 0); k2 = signed_add(k2, GLV_MINUS_B1(), i > 0); }   // v1 = (A1, b1), A1 = B2, b1 < 0
-  if (j) { k1 = signed_add(k1, GLV_A2(), j < 0); k2 = signed_add(k2, GLV_B2(), j < 0); }          // v2 = (A2, B2)
+  for (int t = 0; t < (i < 0 ? -i : i); t++) { k1 = signed_add(k1, GLV_B2(), i < 0); k2 = signed_add(k2, GLV_MINUS_B1(), i > 0); }   // v1 = (A1, b1), A1 = B2, b1 < 0
+  for (int t = 0; t < (j < 0 ? -j : j); t++) { k1 = signed_add(k1, GLV_A2(), j < 0); k2 = signed_add(k2, GLV_B2(), j < 0); }          // v2 = (A2, B2)
   return ladder_plan_from_halves(k1, k2);
 }
 inline LadderPlan make_ladder_plan(const uint8_t scan_sk_le[32]) { return make_ladder_plan_variant(scan_sk_le, 0, 0); }

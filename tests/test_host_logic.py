@@ -115,8 +115,8 @@ def test_decomposition_variants_encode_the_same_scalar_and_the_cheapest_is_chose
     for k in [1, 2, 3, N - 1, N + 1, (1 << 256) - 1] + [rng.randrange(1, 1 << 256) for _ in range(60)]:
         sk = k.to_bytes(32, "little")
         costs = {}
-        for i in (-1, 0, 1):
-            for j in (-1, 0, 1):
+        for i in (-2, -1, 0, 1, 2):          # query_plan.hpp LADDER_SEARCH = 2
+            for j in (-2, -1, 0, 1, 2):
                 p = H.plan_variant(sk, i, j)
                 if p is None:
                     continue
@@ -131,7 +131,7 @@ def test_decomposition_variants_encode_the_same_scalar_and_the_cheapest_is_chose
         assert c["n_dbl"] <= 132 and c["n_add"] <= 60
         saved += costs[(0, 0)] - min(costs.values())
         total += costs[(0, 0)]
-    assert saved > 0.005 * total        # about 1.6 % on average
+    assert saved > 0.01 * total         # about 2 % on average
 
 
 @pytest.mark.parametrize("key", ["pmul_seed42", "pmul_gpu_dumps", "pmul_batch_seed42"])
