@@ -233,12 +233,18 @@ class ArrowScanner {
       return rc;
     }
     memcpy(s.tweaks, k.data + k.begin(base), (size_t)cnt * w);
+    // rebase; a malformed batch (offsets going backwards) is refused here: the kernels index outputs[] with these
+    uint32_t prev = 0, bad = 0;
     if (l.large) {
       const int64_t *o = static_cast<const int64_t *>(l.offsets) + l.offset + base;
-      for (int64_t i = 0; i <= cnt; i++) s.offsets[i] = (uint32_t)(o[i] - o0);
+      for (int64_t i = 0; i <= cnt; i++) { const uint32_t v = (uint32_t)(o[i] - o0); bad |= (uint32_t)(v < prev); s.offsets[i] = prev = v; }
     } else {
       const int32_t *o = static_cast<const int32_t *>(l.offsets) + l.offset + base;
-      for (int64_t i = 0; i <= cnt; i++) s.offsets[i] = (uint32_t)(o[i] - (int32_t)o0);
+      for (int64_t i = 0; i <= cnt; i++) { const uint32_t v = (uint32_t)(o[i] - (int32_t)o0); bad |= (uint32_t)(v < prev); s.offsets[i] = prev = v; }
+    }
+    if (bad || prev != (uint32_t)no) {
+      stg::release(q_, &s);
+      return stg::fail(q_, CUDASP_ERR_ARG, "outputs: list offsets are not monotonically non-decreasing");
     }
     if (no) memcpy(s.outputs, l.values + l.child_offset + o0, no * 8);
     rc = stg::submit(q_, &s, (uint32_t)cnt, no, fmt);

@@ -16,12 +16,13 @@
 #include <atomic>
 #include <condition_variable>
 #include <deque>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
 
 #include "../../include/cudasp.h"
-#include "kernels.cuh"
+#include "launch.hpp"
 #include "query_plan.hpp"
 #include "staging_internal.hpp"
 
@@ -36,12 +37,8 @@ thread_local std::string tl_err;
 const int SLOTS_PER_DEVICE = 6, MAX_SLOTS_PER_DEVICE = 64;   // 6: measured, a 3-deep queue lets the GPU run dry (profiles/r01e)
 const uint32_t EAGER_IDS = 1024;   // ids copied back together with the count
 const uint32_t EAGER_DETAILS = 32; // detail records copied back together with their count
-const uint32_t DETAILS_GRID = 64;  // K8: 64 one-warp blocks stride over the matched rows
 const uint32_t RAMP_DIV = 8;               // ... starting with 1/8 of a piece, doubling (see scan_batch_impl)
 const uint32_t SYNC_PIECE_WAVES = 2;       // cudasp_scan_batch streams a large call in pieces of this many K1 waves
-const int LADDER_BLOCK = 128, LADDER_MINB = 3;
-const int HASH_BLOCK = 128, HASH_MINB = 3;
-const int FINAL_BLOCK = 128;
 const uint32_t INV_ROWS_PER_THREAD = 16;
 
 struct Workspace {          // device-only scratch for one batch in flight
@@ -79,6 +76,7 @@ struct Slot {
   uint8_t *keep_sodd = nullptr;   // cap_rows: parity of its y
   uint32_t det_cap = 0;
   uint32_t n_det = 0;             // after finish()
+  bool det_truncated = false;     // after finish(): K8 found more records than the query's details capacity
   // state
   int state = 0;                  // 0 free, 1 acquired, 2 in flight, 3 result handed out
   uint64_t tag = 0;
@@ -88,6 +86,14 @@ struct Slot {
 
 struct DevCtx {
   int device = 0;
+  // A device is brought up (context, fixed-base table, labels, own stream) by the first slot materialised on it
+  // (ensure_device): a query that never fills a second batch touches one GPU only.
+  bool up = false;
+  std::unique_ptr<std::mutex> init_mu{new std::mutex()};
+  // Users of one workspace are ordered on the device by its free_evt: wait -> launches -> record.  Two host threads
+  // interleaving those three steps on the same workspace (scan_device borrows the slots' workspaces) would both wait on
+  // the OLD event and then run concurrently on the same scratch, so the sequence is made atomic per device.
+  std::unique_ptr<std::mutex> launch_mu{new std::mutex()};
   ge *d_gtab = nullptr;
   ge *d_labels = nullptr;
   cudaStream_t own_stream = nullptr;
@@ -126,6 +132,12 @@ int fail(cudasp_query *q, int code, const std::string &msg) {
   }
   return code;
 }
+// q->mu is already held by the caller (std::mutex is not recursive)
+int fail_locked(cudasp_query *q, int code, const std::string &msg) {
+  tl_err = msg;
+  q->err = msg;
+  return code;
+}
 #define CU(q, call)                                                                                      \
   do {                                                                                                   \
     cudaError_t e_ = (call);                                                                             \
@@ -141,15 +153,15 @@ struct DevGTab {
   uint32_t *bad = nullptr;   // exceptional additions met by the builder (must stay 0)
   bool pending = false, ready = false;
 };
-std::mutex g_gtab_mu;
-std::vector<DevGTab> g_gtab_dev;   // indexed by device ordinal
+const int MAX_DEVICES = 64;
+std::mutex g_gtab_mu[MAX_DEVICES];   // one per device ordinal: devices brought up by different threads build concurrently
+DevGTab g_gtab_dev[MAX_DEVICES];
 
 static void drop_device_gtab(DevGTab &t) {   // after a failed build: leave nothing half-made behind
   cudaFree(t.table); cudaFree(t.seeds); cudaFree(t.bad);
   t = DevGTab();
 }
 int start_device_gtab_locked(cudasp_query *q, int device) {
-  if ((int)g_gtab_dev.size() <= device) g_gtab_dev.resize(device + 1);
   DevGTab &t = g_gtab_dev[device];
   if (t.ready || t.pending) return 0;
   const host::GTabHost &g = host::gtab_host();
@@ -161,9 +173,7 @@ int start_device_gtab_locked(cudasp_query *q, int device) {
     CU(q, cudaMemcpy(t.seeds, g.seeds.firsts.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
     CU(q, cudaMemcpy(t.seeds + GTAB_NWIN, g.seeds.bases.data(), GTAB_NWIN * sizeof(ge), cudaMemcpyHostToDevice));
     CU(q, cudaMemset(t.bad, 0, sizeof(uint32_t)));
-    const uint64_t threads = (uint64_t)(GTAB_NWIN - 1) * (GTAB_ENTRIES / GTAB_EPT) + GTAB_TOP_ENTRIES / GTAB_EPT;
-    k_build_gtab<<<(unsigned)((threads + 127) / 128), 128>>>(t.table, t.seeds, t.seeds + GTAB_NWIN, t.bad);
-    CU(q, cudaGetLastError());
+    CU(q, launch::build_gtab(t.table, t.seeds, t.seeds + GTAB_NWIN, t.bad));
     return 0;
   };
   const int rc = body();
@@ -171,12 +181,9 @@ int start_device_gtab_locked(cudasp_query *q, int device) {
   t.pending = true;
   return 0;
 }
-int start_device_gtab(cudasp_query *q, int device) {
-  std::lock_guard<std::mutex> lk(g_gtab_mu);
-  return start_device_gtab_locked(q, device);
-}
 int get_device_gtab(cudasp_query *q, int device, ge **out) {
-  std::lock_guard<std::mutex> lk(g_gtab_mu);
+  if (device < 0 || device >= MAX_DEVICES) return fail(q, CUDASP_ERR_ARG, "device ordinal out of range");
+  std::lock_guard<std::mutex> lk(g_gtab_mu[device]);
   int rc = start_device_gtab_locked(q, device);
   if (rc) return rc;
   DevGTab &t = g_gtab_dev[device];
@@ -258,17 +265,14 @@ void free_slot(Slot &s) {
   if (s.stream) cudaStreamDestroy(s.stream);
 }
 
-uint32_t inv_threads(uint32_t n) {
-  // elements per Fermat inversion: more of them means less work (270 multiplications per inversion) but a longer
-  // single-thread chain; CUDASP_INV_PER_THREAD is a tuning aid, read once
+uint32_t inv_per_thread() {
+  // elements per Fermat inversion (launch::batch_inv); CUDASP_INV_PER_THREAD is a tuning aid, read once
   static const uint32_t per = [] {
     const char *e = getenv("CUDASP_INV_PER_THREAD");
     const int v = e ? atoi(e) : 0;
     return v > 0 ? (uint32_t)v : INV_ROWS_PER_THREAD;
   }();
-  uint32_t t = (n + per - 1) / per;
-  t = (t + 127u) / 128u * 128u;
-  return std::max<uint32_t>(std::min<uint32_t>(t, n), 1u);
+  return per;
 }
 
 // ---- process-wide cache of staging slots -------------------------------------------------------
@@ -306,10 +310,34 @@ void cache_put(int device, Slot *s) {
   delete s;
 }
 
+// Bring a device of the query up: CUDA context, the process-wide fixed-base table (built on first use), the query's
+// labels, its own stream.  Called by the first slot materialised on the device, from whichever thread asks first;
+// several devices come up concurrently when several threads ask (per-device locks only).
+int ensure_device(cudasp_query *q, int di) {
+  DevCtx &dc = q->devs[di];
+  std::lock_guard<std::mutex> lk(*dc.init_mu);
+  if (dc.up) return 0;
+  int rc = get_device_gtab(q, dc.device, &dc.d_gtab);
+  if (rc) return rc;
+  CU(q, cudaSetDevice(dc.device));
+  if (!dc.own_stream) CU(q, cudaStreamCreateWithFlags(&dc.own_stream, cudaStreamNonBlocking));
+  if (q->n_labels && !dc.d_labels) {
+    CU(q, cudaMalloc(&dc.d_labels, q->n_labels * sizeof(ge)));
+    CU(q, cudaMemcpy(dc.d_labels, q->plan.labels.data(), q->n_labels * sizeof(ge), cudaMemcpyHostToDevice));
+  }
+  {
+    std::lock_guard<std::mutex> lk2(q->mu);       // readers hold q->mu (try_acquire) or init_mu (here)
+    dc.up = true;
+  }
+  return 0;
+}
+
 // A ready-to-use slot for this query on device index `di`: from the cache or freshly allocated.
 int materialise_slot(cudasp_query *q, int di, Slot **out) {
   DevCtx &dc = q->devs[di];
   const uint32_t L = q->n_labels;
+  int rc0 = ensure_device(q, di);
+  if (rc0) return rc0;
   CU(q, cudaSetDevice(dc.device));
   Slot *s = cache_take(dc.device, q->batch_rows, q->max_outputs);
   if (s) {
@@ -334,39 +362,15 @@ int materialise_slot(cudasp_query *q, int di, Slot **out) {
   return 0;
 }
 
-// K1 launch shapes.  Variant 0 is the production default; the others exist for tuning and are selected
-// with the environment variable CUDASP_LADDER_VARIANT (read once per process).
-template <int BLOCK, int MINB, int SYNC, int KEYFMT>
-void launch_ladder_t(const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp, uint8_t *invalid,
-                     cudaStream_t st) {
-  static std::once_flag once;
-  const int smem = LADDER_SMEM_WORDS_PER_THREAD * 4 * BLOCK;
-  std::call_once(once, [&] {
-    cudaFuncSetAttribute(k_ladder<BLOCK, MINB, SYNC, KEYFMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  });
-  const uint32_t grid = (rows + BLOCK - 1) / BLOCK;
-  k_ladder<BLOCK, MINB, SYNC, KEYFMT><<<grid, BLOCK, smem, st>>>(d_tweaks, X, Y, Z, rows, lp, invalid);
-}
 inline size_t key_bytes(int keyfmt) { return keyfmt == CUDASP_KEYS_SEC1_33 ? 33 : 64; }
-int ladder_variant() {
+int ladder_variant() {     // K1 launch shape (k_ladder.cu); 0 = production, others only in tuning builds
   static int v = [] { const char *e = getenv("CUDASP_LADDER_VARIANT"); return e ? atoi(e) : 0; }();
   return v;
 }
-void launch_ladder(int variant, int keyfmt, const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp,
-                   uint8_t *invalid, cudaStream_t st) {
-  if (keyfmt == CUDASP_KEYS_SEC1_33) {   // compressed keys: production shape only
-    launch_ladder_t<128, 4, 1, 1>(d_tweaks, X, Y, Z, rows, lp, invalid, st);
-    return;
-  }
-  switch (variant) {
-    default:
-    case 0: launch_ladder_t<128, 4, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;   // best measured (profiles/r01c)
-#if defined(CSP_LADDER_TUNING)   // the other shapes cost 25 s of ptxas each: only in tuning builds (VARIANT_DEFS=-DCSP_LADDER_TUNING)
-    case 1: launch_ladder_t<128, 3, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
-    case 2: launch_ladder_t<128, 4, 0, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
-    case 3: launch_ladder_t<256, 2, 1, 0>(d_tweaks, X, Y, Z, rows, lp, invalid, st); break;
-#endif
-  }
+cudaError_t launch_ladder(int keyfmt, const uint8_t *d_tweaks, fe *X, fe *Y, fe *Z, uint32_t rows, const LadderParams &lp,
+                          uint8_t *invalid, cudaStream_t st) {
+  return keyfmt == CUDASP_KEYS_SEC1_33 ? launch::ladder_sec1(ladder_variant(), d_tweaks, X, Y, Z, rows, lp, invalid, st)
+                                       : launch::ladder_xy64(ladder_variant(), d_tweaks, X, Y, Z, rows, lp, invalid, st);
 }
 
 struct DetailSink {          // where K3 keeps the shared secrets and K8 appends its records
@@ -413,54 +417,46 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
   uint64_t nl = 0;
   if (d_count) CU(q, cudaMemsetAsync(d_count, 0, 4, st));
   mark();
+  const uint32_t per = inv_per_thread();
   if (!pl.fp.zero_scalar) {
-    launch_ladder(ladder_variant(), keyfmt, d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, w.invalid, st);
+    CU(q, launch_ladder(keyfmt, d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, w.invalid, st));
     mark();
-    const uint32_t T = inv_threads(rows);
-    k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
+    CU(q, launch::batch_inv(w.Z, w.S, rows, per, st));
     nl += 2;
   } else {
     // scan key = 0 (mod n): S is the all-zero pair for every row; compressed keys are still validated (empty op list)
     if (keyfmt == CUDASP_KEYS_SEC1_33) {
-      launch_ladder(ladder_variant(), keyfmt, d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, w.invalid, st);
+      CU(q, launch_ladder(keyfmt, d_tweaks, w.X, w.Y, w.Z, rows, pl.lp, w.invalid, st));
       nl += 1;
     }
     mark();
   }
   mark();
-  {
-    const uint32_t grid = (rows + HASH_BLOCK - 1) / HASH_BLOCK;
-    k_hash_fixedbase<HASH_BLOCK, HASH_MINB><<<grid, HASH_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, dc.d_gtab, pl.fp, dbg_S, dbg_t,
-                                                                         det ? det->keep_sx : nullptr, det ? det->keep_sodd : nullptr);
+  CU(q, launch::hash_fixedbase(w.X, w.Y, w.Z, rows, dc.d_gtab, pl.fp, dbg_S, dbg_t, det ? det->keep_sx : nullptr,
+                               det ? det->keep_sodd : nullptr, st));
+  mark();
+  CU(q, launch::batch_inv(w.Z, w.S, rows, per, st));
+  mark();
+  CU(q, launch::final_base(w.X, w.Y, w.Z, rows, d_outputs, d_off, dc.d_labels, L, w.D, w.flags, d_ids, d_count, d_cands, dbg_P0,
+                           inv_flags, st));
+  nl += 3;
+  mark();
+  if (L) {
+    const uint64_t n64 = (uint64_t)rows * L;
+    if (n64 > 0xffffffffull) return fail(q, CUDASP_ERR_ARG, "rows * labels exceeds 2^32");
+    CU(q, launch::batch_inv(w.D, w.DS, (uint32_t)n64, per, st));
     mark();
-    const uint32_t T = inv_threads(rows);
-    k_batch_inv<<<(T + 127) / 128, 128, 0, st>>>(w.Z, w.S, rows, T);
-    mark();
-    const uint32_t fgrid = (rows + FINAL_BLOCK - 1) / FINAL_BLOCK;
-    k_final_base<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.Z, rows, d_outputs, d_off, dc.d_labels, L, w.D, w.flags,
-                                                            d_ids, d_count, d_cands, dbg_P0, inv_flags);
-    nl += 3;
-    mark();
-    if (L) {
-      const uint64_t n64 = (uint64_t)rows * L;
-      if (n64 > 0xffffffffull) return fail(q, CUDASP_ERR_ARG, "rows * labels exceeds 2^32");
-      const uint32_t n = (uint32_t)n64, T2 = inv_threads(n);
-      k_batch_inv<<<(T2 + 127) / 128, 128, 0, st>>>(w.D, w.DS, n, T2);
-      mark();
-      k_final_labels<FINAL_BLOCK><<<fgrid, FINAL_BLOCK, 0, st>>>(w.X, w.Y, w.D, rows, d_outputs, d_off, dc.d_labels, L, w.flags,
-                                                                d_ids, d_count, d_cands, inv_flags);
-      nl += 2;
-    } else {
-      mark();
-    }
+    CU(q, launch::final_labels(w.X, w.Y, w.D, rows, d_outputs, d_off, dc.d_labels, L, w.flags, d_ids, d_count, d_cands, inv_flags, st));
+    nl += 2;
+  } else {
     mark();
   }
+  mark();
   if (det && d_ids && d_count && d_outputs) {      // K8: the BIP-352 k-loop over the rows that matched (a handful)
-    k_details<<<DETAILS_GRID, 32, 0, st>>>(det->keep_sx, det->keep_sodd, d_ids, d_count, d_outputs, d_off, dc.d_labels, L, dc.d_gtab,
-                                          pl.fp, det->out + 1, reinterpret_cast<uint32_t *>(det->out), det->cap);
+    CU(q, launch::details(det->keep_sx, det->keep_sodd, d_ids, d_count, d_outputs, d_off, dc.d_labels, L, dc.d_gtab, pl.fp,
+                          det->out + 1, reinterpret_cast<uint32_t *>(det->out), det->cap, st));
     nl += 1;
   }
-  CU(q, cudaGetLastError());
   q->launches += nl;
   return 0;
 }
@@ -486,6 +482,7 @@ const char *cudasp_last_error(const cudasp_query *q) {
 void cudasp_query_destroy(cudasp_query *q) {
   if (!q) return;
   for (DevCtx &dc : q->devs) {
+    if (!dc.up && dc.slots.empty()) continue;      // never brought up: no context to touch
     cudaSetDevice(dc.device);
     cudaDeviceSynchronize();
     for (Slot *s : dc.slots) cache_put(dc.device, s);
@@ -522,7 +519,7 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
   if (n_devices <= 0) n_devices = devices ? 0 : visible;
   for (int i = 0; i < n_devices; i++) {
     int d = devices ? devices[i] : i;
-    if (d < 0 || d >= visible) return fail(nullptr, CUDASP_ERR_ARG, "device ordinal out of range");
+    if (d < 0 || d >= visible || d >= MAX_DEVICES) return fail(nullptr, CUDASP_ERR_ARG, "device ordinal out of range");
     devs.push_back(d);
   }
   if (devs.empty()) return fail(nullptr, CUDASP_ERR_ARG, "empty device list");
@@ -535,23 +532,9 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
   q->batch_rows = batch_rows;
   if (max_outputs_per_batch == 0) max_outputs_per_batch = 4ull * batch_rows;
   q->devs.resize(devs.size());
-  for (size_t i = 0; i < devs.size(); i++) {   // first query of the process: every device builds its table, concurrently
-    rc = start_device_gtab(nullptr, devs[i]);
-    if (rc) { cudasp_query_destroy(q); return rc; }
-  }
   for (size_t i = 0; i < devs.size(); i++) {
-    DevCtx &dc = q->devs[i];
-    dc.device = devs[i];
-    rc = get_device_gtab(nullptr, dc.device, &dc.d_gtab);
-    if (rc) { cudasp_query_destroy(q); return rc; }
-    cudaError_t e = cudaSetDevice(dc.device);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&dc.own_stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess && n_labels) {
-      e = cudaMalloc(&dc.d_labels, n_labels * sizeof(ge));
-      if (e == cudaSuccess) e = cudaMemcpy(dc.d_labels, q->plan.labels.data(), n_labels * sizeof(ge), cudaMemcpyHostToDevice);
-    }
-    if (e != cudaSuccess) { cudasp_query_destroy(q); return fail(nullptr, CUDASP_ERR_CUDA, cudaGetErrorString(e)); }
-    dc.max_slots = slots_per_device;
+    q->devs[i].device = devs[i];
+    q->devs[i].max_slots = slots_per_device;
   }
   q->max_outputs = max_outputs_per_batch;
   {
@@ -562,16 +545,26 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
     q->piece_rows = (uint32_t)sms * 4u * 128u * waves;
   }
   q->all_slots.reserve(devs.size() * slots_per_device);   // never reallocates: ids stay valid without the lock
-  for (size_t i = 0; i < devs.size(); i++) {             // one slot per device now, the rest on demand
+  // Only the FIRST device is brought up here (context, fixed-base table, one slot), so that key and device errors surface
+  // at creation; the others come up when a slot on them is first acquired (try_acquire): a query of a few rows -- every
+  // statement of test/sql/cudasp.test -- costs one device's bring-up, not all of them (the reference's once-per-device
+  // init is 16 KB, gsv.h:1094-1122; this build's is a 2.95 GB table, so it must not be paid where it is not used).
+  {
     Slot *s = nullptr;
-    rc = materialise_slot(q, (int)i, &s);
+    rc = materialise_slot(q, 0, &s);
     if (rc) { std::string m = tl_err; cudasp_query_destroy(q); return fail(nullptr, rc, m); }
     s->id = (uint32_t)q->all_slots.size();
-    q->devs[i].slots.push_back(s);
+    q->devs[0].slots.push_back(s);
     q->all_slots.push_back(s);
   }
   *out = q;
   return CUDASP_OK;
+}
+
+int cudasp_device_sm_count(int device) {
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return sms;
 }
 
 void cudasp_release_cached_memory(void) {
@@ -623,11 +616,14 @@ Slot *try_acquire(cudasp_query *q, int *err) {
         }
       }
     }
+    // grow where the fewest slots are; a device that is not up yet counts as if it had two, so that a caller
+    // that never needs more than two batches in flight stays on the devices already paid for
     size_t best = SIZE_MAX;
     for (size_t k = 0; k < nd; k++) {
       DevCtx &dc = q->devs[(q->rr + k) % nd];
       const size_t have = dc.slots.size() + dc.pending;
-      if (have < dc.max_slots && have < best) { best = have; grow_dev = (int)((q->rr + k) % nd); }
+      const size_t key = have + ((dc.up || have) ? 0 : 2);
+      if (have < dc.max_slots && key < best) { best = key; grow_dev = (int)((q->rr + k) % nd); }
     }
     if (grow_dev < 0) return nullptr;
     q->devs[grow_dev].pending++;
@@ -700,10 +696,12 @@ int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t
     if (n_outputs) CU(q, cudaMemcpyAsync(s->d_outputs, s->h_outputs, n_outputs * 8, cudaMemcpyHostToDevice, st));
   }
   if (trace) cudaEventRecord(s->tr[1], st);
+  std::lock_guard<std::mutex> launch_lk(*dc.launch_mu);     // wait -> launches -> record is atomic per device (see DevCtx)
   CU(q, cudaStreamWaitEvent(st, s->ws.free_evt, 0));
   DetailSink sink{};
   const bool details = q->details_cap != 0;
   s->n_det = 0;
+  s->det_truncated = false;
   if (details) {
     int r = ensure_details(q, *s);
     if (r) return r;
@@ -745,8 +743,11 @@ int finish(cudasp_query *q, Slot *s, uint32_t *n_matches) {
   std::sort(s->h_result + 1, s->h_result + 1 + n);
   *n_matches = n;
   if (q->details_cap && s->h_det && s->rows) {
-    const uint32_t nd = *reinterpret_cast<const uint32_t *>(s->h_det);
-    if (nd > q->details_cap) return fail(q, CUDASP_ERR_STATE, "more match details than max_details_per_batch: raise it");
+    uint32_t nd = *reinterpret_cast<const uint32_t *>(s->h_det);
+    // K8 counts every record but stores only the first details_cap: the matches themselves are complete either way, so the
+    // batch is delivered with the records that fit and the caller is told (CUDASP_RESULT_DETAILS_TRUNCATED)
+    s->det_truncated = nd > q->details_cap;
+    nd = std::min(nd, q->details_cap);
     if (nd > EAGER_DETAILS) {
       CU(q, cudaMemcpyAsync(s->h_det + 1 + EAGER_DETAILS, s->d_det + 1 + EAGER_DETAILS, ((size_t)nd - EAGER_DETAILS) * sizeof(MatchDetail),
                             cudaMemcpyDeviceToHost, s->stream));
@@ -851,6 +852,11 @@ int cudasp_submit_slot_fmt(cudasp_query *q, const cudasp_slot *slot, uint32_t ro
   if (s->state != 1) return fail(q, CUDASP_ERR_STATE, "slot was not acquired");
   if (rows > s->cap_rows || n_outputs > s->cap_outputs) return fail(q, CUDASP_ERR_ARG, "rows/outputs exceed the slot capacity");
   if (rows && s->h_off[rows] != n_outputs) return fail(q, CUDASP_ERR_ARG, "out_offsets[rows] != n_outputs");
+  if (rows) {      // the kernels index outputs[] with these: zero-based and monotonic, or the batch is refused (1.2 MB pass)
+    uint32_t prev = s->h_off[0], bad = prev;
+    for (uint32_t i = 1; i <= rows; i++) { const uint32_t v = s->h_off[i]; bad |= (uint32_t)(v < prev); prev = v; }
+    if (bad) return fail(q, CUDASP_ERR_ARG, "out_offsets must start at 0 and be monotonically non-decreasing");
+  }
   int rc = submit(q, s, rows, n_outputs, tag, key_format);
   if (rc) return rc;
   std::lock_guard<std::mutex> lk(q->mu);
@@ -859,31 +865,41 @@ int cudasp_submit_slot_fmt(cudasp_query *q, const cudasp_slot *slot, uint32_t ro
   return CUDASP_OK;
 }
 
+// Hands out a finished batch.  ANY in-flight batch whose `done` event has fired qualifies, not only the oldest: with
+// several devices (or several streams of one device) a finished batch queued behind an unfinished one would otherwise
+// keep its slot from being recycled (head-of-line blocking).  Blocking mode falls back to waiting for the oldest.
+// On an error after the batch left the in-flight list, *r still names the slot (tag, slot_id, rows; no matches) so
+// that the caller can release it -- otherwise the slot would be lost and a later acquire could block forever.
 static int take_result(cudasp_query *q, cudasp_result *r, bool block) {
   if (!q || !r) return fail(q, CUDASP_ERR_ARG, "NULL argument");
   Slot *s = nullptr;
   {
     std::lock_guard<std::mutex> lk(q->mu);
     if (q->inflight.empty()) return 0;
-    s = q->inflight.front();
-    if (!block) {
-      cudaSetDevice(q->devs[s->dev_index].device);
-      cudaError_t e = cudaEventQuery(s->done);
-      if (e == cudaErrorNotReady) return 0;
-      if (e != cudaSuccess) { q->err = cudaGetErrorString(e); tl_err = q->err; return CUDASP_ERR_CUDA; }
+    for (auto it = q->inflight.begin(); it != q->inflight.end(); ++it) {
+      const cudaError_t e = cudaEventQuery((*it)->done);
+      if (e == cudaErrorNotReady) continue;
+      if (e != cudaSuccess) return fail_locked(q, CUDASP_ERR_CUDA, cudaGetErrorString(e));
+      s = *it;
+      q->inflight.erase(it);
+      break;
     }
-    q->inflight.pop_front();
+    if (!s) {
+      if (!block) return 0;
+      s = q->inflight.front();
+      q->inflight.pop_front();
+    }
     s->state = 3;
   }
   uint32_t n = 0;
-  int rc = finish(q, s, &n);
-  if (rc) return rc;
+  const int rc = finish(q, s, &n);
   r->tag = s->tag;
   r->slot_id = s->id;
   r->rows = s->rows;
-  r->n_matches = n;
-  r->match_ids = s->h_result + 1;
-  return 1;
+  r->flags = s->det_truncated ? CUDASP_RESULT_DETAILS_TRUNCATED : 0u;
+  r->n_matches = rc ? 0 : n;
+  r->match_ids = rc ? nullptr : s->h_result + 1;
+  return rc ? rc : 1;
 }
 int cudasp_poll(cudasp_query *q, cudasp_result *r) { return take_result(q, r, false); }
 int cudasp_wait(cudasp_query *q, cudasp_result *r) { return take_result(q, r, true); }
@@ -925,7 +941,7 @@ int cudasp_query_enable_details(cudasp_query *q, uint32_t max_details_per_batch)
   if (!q) return fail(q, CUDASP_ERR_ARG, "NULL query");
   std::lock_guard<std::mutex> lk(q->mu);
   for (Slot *s : q->all_slots)
-    if (s->state != 0) return fail(q, CUDASP_ERR_STATE, "enable details before the first batch is acquired");
+    if (s->state != 0) return fail_locked(q, CUDASP_ERR_STATE, "enable details before the first batch is acquired");
   q->details_cap = max_details_per_batch ? max_details_per_batch : std::min<uint32_t>(q->batch_rows, 65536u);
   return CUDASP_OK;
 }
@@ -965,6 +981,7 @@ static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_f
     const double tw = trace ? now() : 0;
     int r = finish(q, p.s, &n);
     if (trace) t_wait += now() - tw;
+    if (!r && p.s->det_truncated) r = fail(q, CUDASP_ERR_STATE, "more match details than max_details_per_batch: raise it");
     if (!r) {
       for (uint32_t i = 0; i < n; i++) match_ids[total + i] = p.base + p.s->h_result[1 + i];
       total += n;
@@ -1004,6 +1021,11 @@ static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_f
     if (rc) break;
     s->internal = true;
     const uint32_t o0 = out_offsets ? out_offsets[base] : 0;
+    if (out_offsets && out_offsets[base + cnt] < o0) {
+      release_slot(q, s);
+      rc = fail(q, CUDASP_ERR_ARG, "out_offsets is not monotonically non-decreasing");
+      break;
+    }
     const uint64_t no = out_offsets ? (uint64_t)(out_offsets[base + cnt] - o0) : 0;
     if (no > s->cap_outputs) {
       cudaSetDevice(q->devs[s->dev_index].device);
@@ -1014,7 +1036,14 @@ static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_f
     const double tc = trace ? now() : 0;
     memcpy(s->h_tweaks, tweak_keys + (size_t)base * kb, (size_t)cnt * kb);
     if (out_offsets) {
-      for (uint32_t i = 0; i <= cnt; i++) s->h_off[i] = out_offsets[base + i] - o0;
+      // rebase, and refuse a non-monotonic offset array: K5/K7/K8 index the outputs with these, unchecked
+      uint32_t prev = 0, bad = 0;
+      for (uint32_t i = 0; i <= cnt; i++) {
+        const uint32_t v = out_offsets[base + i] - o0;
+        bad |= (uint32_t)(v < prev);
+        s->h_off[i] = prev = v;
+      }
+      if (bad) { release_slot(q, s); rc = fail(q, CUDASP_ERR_ARG, "out_offsets is not monotonically non-decreasing"); break; }
       if (no) memcpy(s->h_outputs, outputs + o0, no * 8);
     } else {
       memset(s->h_off, 0, ((size_t)cnt + 1) * 4);
@@ -1052,17 +1081,18 @@ int cudasp_scan_device(cudasp_query *q, int device, const uint8_t *d_tweak_keys,
   if (!dc) return fail(q, CUDASP_ERR_ARG, "device is not part of this query");
   if (rows > q->batch_rows) return fail(q, CUDASP_ERR_ARG, "rows exceed batch_rows (split the call)");
   if (rows && (!d_tweak_keys || !d_match_ids || !d_n_matches)) return fail(q, CUDASP_ERR_ARG, "NULL device pointer");
+  // borrow the scratch of one of the device's slots, round robin; ordering between users of the
+  // same scratch is enforced with its free_evt (under the device's launch lock), so any stream may be used.
+  int rc0 = ensure_slots(q, (int)(dc - q->devs.data()), 3);   // also brings the device up
+  if (rc0) return rc0;
   CU(q, cudaSetDevice(device));
   cudaStream_t st = stream ? (cudaStream_t)stream : dc->own_stream;
-  // borrow the scratch of one of the device's slots, round robin; ordering between users of the
-  // same scratch is enforced with its free_evt, so any stream may be used.
-  int rc0 = ensure_slots(q, (int)(dc - q->devs.data()), 3);
-  if (rc0) return rc0;
   Workspace *w;
   {
     std::lock_guard<std::mutex> lk(q->mu);
     w = &dc->slots[dc->next_ws++ % dc->slots.size()]->ws;
   }
+  std::lock_guard<std::mutex> launch_lk(*dc->launch_mu);
   CU(q, cudaStreamWaitEvent(st, w->free_evt, 0));
   int rc = launch_pipeline(q, *dc, *w, d_tweak_keys, d_outputs, d_out_offsets, rows, d_match_ids, d_n_matches, st, nullptr,
                            nullptr, nullptr, nullptr);
@@ -1083,14 +1113,18 @@ int cudasp_profile_stages(cudasp_query *q, int device, const uint8_t *d_tweak_ke
   CU(q, cudaSetDevice(device));
   cudaEvent_t ev[8];
   for (int i = 0; i < 8; i++) CU(q, cudaEventCreate(&ev[i]));
+  int rc0 = ensure_slots(q, (int)(dc - q->devs.data()), 1);
+  if (rc0) return rc0;
   Workspace &w = dc->slots[0]->ws;
   cudaStream_t st = dc->own_stream;
+  std::unique_lock<std::mutex> launch_lk(*dc->launch_mu);
   CU(q, cudaStreamWaitEvent(st, w.free_evt, 0));
   const char *kf = getenv("CUDASP_PROFILE_KEYFMT");      // tuning aid: "1" = d_tweak_keys holds 33-byte SEC1 keys
   int rc = launch_pipeline(q, *dc, w, d_tweak_keys, d_outputs, d_out_offsets, rows, d_match_ids, d_n_matches, st, nullptr, nullptr,
                            nullptr, nullptr, ev, kf && kf[0] == '1' ? CUDASP_KEYS_SEC1_33 : CUDASP_KEYS_XY64);
   if (!rc) {
     cudaEventRecord(w.free_evt, st);
+    launch_lk.unlock();
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) rc = fail(q, CUDASP_ERR_CUDA, cudaGetErrorString(e));
     for (int i = 0; i < 7 && !rc; i++) cudaEventElapsedTime(&stage_ms[i], ev[i], ev[i + 1]);
@@ -1120,11 +1154,14 @@ static int scan_debug(cudasp_query *q, const uint8_t *tweak_keys, uint32_t rows,
       if (t_be) CU(q, cudaMalloc(&d_t, (size_t)cnt * 32));
       if (P0_le) CU(q, cudaMalloc(&d_P, (size_t)cnt * 64));
       CU(q, cudaMemcpyAsync(s->d_tweaks, tweak_keys + (size_t)base * kb, (size_t)cnt * kb, cudaMemcpyHostToDevice, s->stream));
-      CU(q, cudaStreamWaitEvent(s->stream, s->ws.free_evt, 0));
-      int r = launch_pipeline(q, dc, s->ws, s->d_tweaks, nullptr, nullptr, cnt, nullptr, nullptr, s->stream, d_c, d_S, d_t, d_P, nullptr,
-                              keyfmt);
-      if (r) return r;
-      CU(q, cudaEventRecord(s->ws.free_evt, s->stream));
+      {
+        std::lock_guard<std::mutex> launch_lk(*dc.launch_mu);
+        CU(q, cudaStreamWaitEvent(s->stream, s->ws.free_evt, 0));
+        int r = launch_pipeline(q, dc, s->ws, s->d_tweaks, nullptr, nullptr, cnt, nullptr, nullptr, s->stream, d_c, d_S, d_t, d_P, nullptr,
+                                keyfmt);
+        if (r) return r;
+        CU(q, cudaEventRecord(s->ws.free_evt, s->stream));
+      }
       if (cands) CU(q, cudaMemcpyAsync(cands + (size_t)base * (1 + L), d_c, (size_t)cnt * (1 + L) * 8, cudaMemcpyDeviceToHost, s->stream));
       if (S_le) CU(q, cudaMemcpyAsync(S_le + (size_t)base * 64, d_S, (size_t)cnt * 64, cudaMemcpyDeviceToHost, s->stream));
       if (t_be) CU(q, cudaMemcpyAsync(t_be + (size_t)base * 32, d_t, (size_t)cnt * 32, cudaMemcpyDeviceToHost, s->stream));
@@ -1184,8 +1221,7 @@ int cudasp_test_field(int device, int op, const uint8_t *a, const uint8_t *b, ui
     CU(nullptr, cudaMalloc(&dout, (size_t)n * 32));
     CU(nullptr, cudaMemcpy(da, a, (size_t)n * 32, cudaMemcpyHostToDevice));
     CU(nullptr, cudaMemcpy(db, b, (size_t)n * 32, cudaMemcpyHostToDevice));
-    k_test_field<<<(n + 127) / 128, 128>>>(op, da, db, dout, n);
-    CU(nullptr, cudaGetLastError());
+    CU(nullptr, launch::test_field(op, da, db, dout, n));
     CU(nullptr, cudaMemcpy(out, dout, (size_t)n * 32, cudaMemcpyDeviceToHost));
     return 0;
   };

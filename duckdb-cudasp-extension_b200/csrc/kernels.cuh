@@ -60,10 +60,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_ladder(const uint8_t *__restric
   store_fe(outZ + row, acc.z);
 }
 
+// The non-template kernels below are DEFINED only in the translation unit that launches them (k_stages.cu).
+#if defined(CSP_DEFINE_STAGE_KERNELS)
 // ---------------------------------------------------------------- K2/K4/K6: batch inversion
 __global__ void __launch_bounds__(128) k_batch_inv(fe *__restrict__ vals, fe *__restrict__ scratch, uint32_t n, uint32_t T) {
   batch_inv_thread(vals, scratch, n, T, blockIdx.x * blockDim.x + threadIdx.x);
 }
+
+#endif  // CSP_DEFINE_STAGE_KERNELS
 
 // ---------------------------------------------------------------- K3: hash, t*G, + B_spend (in place)
 template <int BLOCK, int MINB>
@@ -197,6 +201,7 @@ __global__ void __launch_bounds__(BLOCK) k_final_labels(const fe *__restrict__ X
   if (match_ids) append_match(live && hit, row, match_ids, n_matches);
 }
 
+#if defined(CSP_DEFINE_STAGE_KERNELS)
 // ---------------------------------------------------------------- field KAT kernel (tests)
 __global__ void k_test_field(int op, const fe *__restrict__ a, const fe *__restrict__ b, fe *__restrict__ out, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -264,5 +269,7 @@ __global__ void __launch_bounds__(128) k_build_gtab(ge *__restrict__ table, cons
   load_fe_ro(b.x, &bases[w].x); load_fe_ro(b.y, &bases[w].y);
   if (!gtab_chunk(table + (size_t)w * GTAB_ENTRIES + d0, f, b, d0)) atomicAdd(bad, 1u);
 }
+
+#endif  // CSP_DEFINE_STAGE_KERNELS
 
 }  // namespace csp

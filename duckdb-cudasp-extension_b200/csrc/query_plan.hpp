@@ -55,8 +55,10 @@ inline bool point_from_blob(HPoint &p, const uint8_t b[64]) {
 }
 
 // Checks that the op list never adds a point to itself or its negative: simulate the scalar
-// (a + b*lambda mod n) the accumulator holds before every ADD.
-inline bool ladder_plan_is_regular(const LadderPlan &p) {
+// (a + b*lambda mod n) the accumulator holds before every ADD.  With `expect` given, the scalar the whole list
+// evaluates to must also equal it (k = scan_sk mod n): a wrong lattice constant or sign in a decomposition variant
+// would otherwise give a wrong shared secret for every row without any error.
+inline bool ladder_plan_is_regular(const LadderPlan &p, const Big *expect = nullptr) {
   const Big n = N_ORDER(), lam = LAMBDA();
   Big v;  // accumulator scalar mod n
   for (int i = 0; i < p.nops; i++) {
@@ -72,6 +74,7 @@ inline bool ladder_plan_is_regular(const LadderPlan &p) {
     }
     v = mod(add(v, d), n);
   }
+  if (expect && cmp(v, *expect) != 0) return false;
   return !v.is_zero();
 }
 
@@ -85,6 +88,7 @@ inline int make_query_plan(QueryPlan &q, const uint8_t sk[32], const uint8_t spe
   // one whose interleaved NAFs cost K1 the fewest field multiplications -- 2 % fewer on average than the balanced split.
   // Candidates are tried cheapest first; the regularity check (big-number arithmetic) runs until one passes.
   LadderPlan lp = make_ladder_plan(sk);
+  const Big k_mod_n = mod(Big::from_le(sk, 32), N_ORDER());
   if (!lp.zero) {
     struct Cand { int cost, i, j; };
     std::vector<Cand> cands;
@@ -100,15 +104,14 @@ inline int make_query_plan(QueryPlan &q, const uint8_t sk[32], const uint8_t spe
     });
     for (const Cand &c : cands) {
       LadderPlan p = (c.i || c.j) ? make_ladder_plan_variant(sk, c.i, c.j) : lp;
-      if (ladder_plan_is_regular(p)) { lp = p; break; }
+      if (ladder_plan_is_regular(p, &k_mod_n)) { lp = p; break; }   // a variant that does not evaluate to k is skipped
     }
   }
   q.n_dbl = lp.n_dbl;
   q.n_add = lp.n_add;
   if (!lp.zero) {
     if (lp.nops > LADDER_MAX_OPS_DEV) { err = "internal: ladder op list too long"; return -4; }
-    if (!ladder_plan_is_regular(lp)) { err = "scan_private_key yields a degenerate ladder schedule"; return -4; }
-    // the schedule must reproduce k: checked by ladder_plan_is_regular's final scalar in tests
+    if (!ladder_plan_is_regular(lp, &k_mod_n)) { err = "scan_private_key yields a degenerate ladder schedule"; return -4; }
     memcpy(q.lp.ops, lp.ops, (size_t)lp.nops);
     q.lp.nops = lp.nops;
   }

@@ -227,12 +227,14 @@ static unique_ptr<GlobalTableFunctionState> CudaspScanInit(ClientContext &contex
 	auto state = make_uniq<CudaspScanState>();
 	int n_dev = cudasp_device_count();
 	if (n_dev <= 0) {
-		throw IOException("cudasp_scan: no CUDA device available (%s)", cudasp_last_error(nullptr));
+		throw IOException("cudasp_scan: no CUDA device available (this extension has no CPU path)");
 	}
 	idx_t threads = MaxValue<idx_t>(1, NumericCast<idx_t>(TaskScheduler::GetScheduler(context).NumberOfThreads()));
 	// rows per GPU batch: batch_size, cut down when there are many workers per GPU (see steady_limit)
 	{
-		const uint64_t wave = 148ull * 4 * 128;
+		// one full wave of the ladder kernel: SMs x 4 resident blocks x 128 rows (148 SMs on B200)
+		const int sms = cudasp_device_sm_count(0);
+		const uint64_t wave = (uint64_t)(sms > 0 ? sms : 148) * 4 * 128;
 		const uint64_t share = (uint64_t)bind.batch_size * 2 * (uint64_t)n_dev / threads;
 		state->steady_limit = (uint32_t)MinValue<uint64_t>(bind.batch_size, MaxValue<uint64_t>(wave, share));
 	}

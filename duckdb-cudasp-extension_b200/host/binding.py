@@ -28,7 +28,7 @@ class Slot(C.Structure):
 
 class Result(C.Structure):
     _fields_ = [("tag", C.c_uint64), ("slot_id", C.c_uint32), ("rows", C.c_uint32), ("n_matches", C.c_uint32),
-                ("match_ids", u32p)]
+                ("flags", C.c_uint32), ("match_ids", u32p)]
 
 
 class MatchDetail(C.Structure):      # include/cudasp.h cudasp_match_detail
@@ -45,7 +45,8 @@ EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "c
            "cudasp_scan_device", "cudasp_profile_stages", "cudasp_scan_candidates", "cudasp_scan_intermediates", "cudasp_test_field",
            "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory",
            "cudasp_scan_batch_fmt", "cudasp_submit_slot_fmt", "cudasp_scan_candidates_fmt",
-           "cudasp_query_enable_details", "cudasp_result_details", "cudasp_scan_batch_details", "cudasp_debug_gtab"]
+           "cudasp_query_enable_details", "cudasp_result_details", "cudasp_scan_batch_details", "cudasp_debug_gtab",
+           "cudasp_device_sm_count"]
 
 
 def lib():
@@ -80,6 +81,7 @@ def lib():
         L.cudasp_scan_intermediates.argtypes = [vp, vp, C.c_uint32, vp, vp, vp]
         L.cudasp_test_field.argtypes = [C.c_int, C.c_int, vp, vp, vp, C.c_uint32]
         L.cudasp_debug_gtab.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, vp]
+        L.cudasp_device_sm_count.argtypes = [C.c_int]
         L.cudasp_launch_count.argtypes = [vp]
         L.cudasp_launch_count.restype = C.c_uint64
         L.cudasp_query_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 5

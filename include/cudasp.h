@@ -57,12 +57,14 @@ const char *cudasp_last_error(const cudasp_query *q);
 
 /* Once-per-query setup.  Replaces the per-batch key marshalling of ProcessBatch/LaunchBatchScan
  * (src/cudasp_extension.cu:277-297, src/cudasp_gpu.cu:445-669) and Solver::initialize
- * (gECC gsv.h:1094-1122): recodes the fixed scan key (GLV + wNAF), uploads the fixed-base table,
- * allocates every device/pinned buffer for `batch_rows`-row batches on each listed device.
+ * (gECC gsv.h:1094-1122): recodes the fixed scan key (GLV + wNAF) and brings the FIRST listed device up
+ * (CUDA context, the process-wide fixed-base table -- built on the device on first use --, one staging slot).
+ * The other devices are brought up when a staging slot on them is first needed, so a query of a few rows
+ * touches one GPU only; a device that fails to come up is reported by the acquire/scan call that needed it.
  *   devices == NULL  -> use devices 0..n_devices-1;  n_devices == 0 -> all visible devices.
  *   max_outputs_per_batch == 0 -> 4 * batch_rows (grown on demand by the synchronous call; a streaming
  *   producer cuts a batch early when the next row's outputs would not fit).
- * Staging slots are materialised on demand (one per device at creation) and are parked in a process-wide
+ * Staging slots are materialised on demand (one at creation) and are parked in a process-wide
  * cache by cudasp_query_destroy, so later queries do not pay the pinned/device allocations again. */
 int cudasp_query_create(const uint8_t scan_private_key[32], const uint8_t spend_public_key[64],
                         const uint8_t *label_keys /* n_labels * 64 B */, uint32_t n_labels,
@@ -76,6 +78,10 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
                            const uint8_t *label_keys, uint32_t n_labels, const int *devices, int n_devices,
                            uint32_t batch_rows, uint64_t max_outputs_per_batch, uint32_t slots_per_device,
                            cudasp_query **out);
+
+/* Streaming multiprocessor count of a device (no context is created): hosts size their batches in whole waves of the
+ * ladder kernel (SMs x 4 blocks x 128 rows). 0 on error. */
+int cudasp_device_sm_count(int device);
 
 /* Frees the staging slots parked by destroyed queries (see above). */
 void cudasp_release_cached_memory(void);
@@ -114,10 +120,17 @@ typedef struct cudasp_result {
   uint32_t slot_id;
   uint32_t rows;
   uint32_t n_matches;
+  uint32_t flags;            /* CUDASP_RESULT_* */
   const uint32_t *match_ids; /* pinned; ascending row indices within the slot; valid until release */
 } cudasp_result;
+/* match details were enabled and the batch produced more records than max_details_per_batch: match_ids are complete,
+ * cudasp_result_details returns the records that fit */
+#define CUDASP_RESULT_DETAILS_TRUNCATED 1u
 
-/* Blocks until a staging slot is free (a slot is recycled by cudasp_release_result). */
+/* Preconditions the library checks on submit: out_offsets[0] == 0, out_offsets non-decreasing,
+ * out_offsets[rows] == n_outputs (the kernels index outputs[] with them).
+ * Threading: every function below may be called concurrently on one handle.
+ * Blocks until a staging slot is free (a slot is recycled by cudasp_release_result). */
 int cudasp_acquire_slot(cudasp_query *q, cudasp_slot *slot);
 /* Non-blocking variant: returns 1 and fills *slot, or 0 when every slot is busy. */
 int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot);
@@ -125,16 +138,21 @@ int cudasp_try_acquire_slot(cudasp_query *q, cudasp_slot *slot);
 int cudasp_submit_slot(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag);
 int cudasp_submit_slot_fmt(cudasp_query *q, const cudasp_slot *slot, uint32_t rows, uint64_t n_outputs, uint64_t tag,
                            int key_format);
-/* Returns 1 and fills *r when a finished batch is available, 0 when none is finished yet. */
+/* Returns 1 and fills *r when a finished batch is available (ANY finished batch, whatever the submit order: a batch
+ * finished on one device is not held back by an older one still running on another), 0 when none is finished yet.
+ * On a negative return after a batch was taken, r->tag / slot_id / rows are filled (n_matches = 0) so that the caller
+ * can hand the slot back with cudasp_release_result. */
 int cudasp_poll(cudasp_query *q, cudasp_result *r);
-/* Blocks for the oldest in-flight batch; returns 1 with *r filled, or 0 when nothing is in flight. */
+/* Same, but blocks (for the oldest in-flight batch) when none has finished; returns 0 only when nothing is in flight. */
 int cudasp_wait(cudasp_query *q, cudasp_result *r);
 /* Hand the slot of a consumed result back to the pool. */
 int cudasp_release_result(cudasp_query *q, const cudasp_result *r);
 
 /* ---- device-resident entry (benchmarks; hosts that already hold columns in HBM) -------------
  * All pointers are device pointers on `device` (which must be one of the query's devices);
- * `stream` is a cudaStream_t (0 = the query's own stream for that device).  Asynchronous.
+ * `stream` is a cudaStream_t (0 = the query's own stream for that device).  Asynchronous.  Thread-safe: the scratch it
+ * borrows from the device's staging slots is handed from user to user with an event, recorded under a per-device lock.
+ * d_out_offsets must be zero-based and non-decreasing (not checked: it lives on the device).
  * d_match_ids: capacity >= rows; *d_n_matches is reset and then holds the count; ids unordered. */
 int cudasp_scan_device(cudasp_query *q, int device, const uint8_t *d_tweak_keys, const int64_t *d_outputs,
                        const uint32_t *d_out_offsets, uint32_t rows, uint32_t *d_match_ids,

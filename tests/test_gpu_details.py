@@ -119,3 +119,37 @@ def test_details_capacity_overflow_is_reported(M):
             q.scan_batch_details(T["tweaks"], T["outputs"], T["offsets"], capacity=3)
         ids, recs = q.scan_batch_details(T["tweaks"], T["outputs"], T["offsets"])
         assert len(recs) == sum(len(v) for v in want.values())
+
+
+def test_streaming_details_overflow_is_flagged_not_lost(M):
+    """A batch with more detail records than max_details_per_batch still delivers its (complete) matches through the streaming
+    API, flagged CUDASP_RESULT_DETAILS_TRUNCATED, and its slot can be released (it used to fail without naming the slot)."""
+    import ctypes as C
+    from importlib import import_module
+    B = import_module("cudasp_b200.host.binding")
+    T, want = build_table(600, 0, 55, 40)
+    L = M.lib()
+    with M.Query(T["sk"], T["spend"], [], batch_rows=600) as q:
+        q.enable_details(8)
+        s = B.Slot()
+        assert L.cudasp_acquire_slot(q.handle, C.byref(s)) == 0
+        # enabling details again while a slot is held is a state error, not a self-deadlock on the query mutex
+        assert L.cudasp_query_enable_details(q.handle, 16) == B.ERR_STATE
+        assert b"before the first batch" in L.cudasp_last_error(q.handle)
+        n_out = int(T["offsets"][600])
+        C.memmove(s.tweak_keys, T["tweaks"].ctypes.data, 600 * 64)
+        C.memmove(s.outputs, T["outputs"].ctypes.data, 8 * n_out)
+        C.memmove(s.out_offsets, T["offsets"].ctypes.data, 601 * 4)
+        assert L.cudasp_submit_slot(q.handle, C.byref(s), 600, n_out, 7) == 0
+        r = B.Result()
+        assert L.cudasp_wait(q.handle, C.byref(r)) == 1
+        assert r.tag == 7 and r.flags & 1
+        assert [r.match_ids[i] for i in range(r.n_matches)] == T["expected"].tolist()
+        d, n = C.POINTER(B.MatchDetail)(), C.c_uint32(0)
+        assert L.cudasp_result_details(q.handle, C.byref(r), C.byref(d), C.byref(n)) == 0
+        assert n.value == 8
+        assert L.cudasp_release_result(q.handle, C.byref(r)) == 0
+        assert L.cudasp_acquire_slot(q.handle, C.byref(s)) == 0          # the slot came back
+        assert L.cudasp_submit_slot(q.handle, C.byref(s), 0, 0, 8) == 0
+        assert L.cudasp_wait(q.handle, C.byref(r)) == 1 and r.flags == 0
+        assert L.cudasp_release_result(q.handle, C.byref(r)) == 0

@@ -207,3 +207,34 @@ def test_streaming_api_and_device_entry(M):
         torch.cuda.synchronize()
         n = int(d_n.item())
         assert sorted(d_ids[:n].tolist()) == [int(x) for x in T["expected"] if x < 1000]
+
+
+def test_malformed_offsets_are_refused(M):
+    """out_offsets index the outputs array inside K5/K7/K8: a non-monotonic or non-zero-based array is an argument error on
+    every entry that takes host offsets, never an out-of-bounds device read."""
+    import ctypes as C
+    from importlib import import_module
+    B = import_module("cudasp_b200.host.binding")
+    T = synth.make_table(300, 99, n_labels=0, n_base=3, n_per_label=0, batch_rows=300)
+    L = M.lib()
+    with M.Query(T["sk"], T["spend"], [], batch_rows=300) as q:
+        bad = T["offsets"].copy()
+        bad[100], bad[101] = bad[101] + 5, bad[100]
+        with pytest.raises(M.CudaspError, match="monoton"):
+            q.scan_batch(T["tweaks"], T["outputs"], bad)
+        assert np.array_equal(q.scan_batch(T["tweaks"], T["outputs"], T["offsets"]), T["expected"])
+        s = B.Slot()
+        assert L.cudasp_acquire_slot(q.handle, C.byref(s)) == 0
+        n_out = int(T["offsets"][300])
+        C.memmove(s.tweak_keys, T["tweaks"].ctypes.data, 300 * 64)
+        C.memmove(s.outputs, T["outputs"].ctypes.data, 8 * n_out)
+        shifted = (T["offsets"] + 1).astype(np.uint32)
+        shifted[300] = n_out
+        C.memmove(s.out_offsets, shifted.ctypes.data, 301 * 4)
+        assert L.cudasp_submit_slot(q.handle, C.byref(s), 300, n_out, 0) == B.ERR_ARG
+        C.memmove(s.out_offsets, T["offsets"].ctypes.data, 301 * 4)
+        assert L.cudasp_submit_slot(q.handle, C.byref(s), 300, n_out, 0) == 0
+        r = B.Result()
+        assert L.cudasp_wait(q.handle, C.byref(r)) == 1
+        assert [r.match_ids[i] for i in range(r.n_matches)] == T["expected"].tolist()
+        assert L.cudasp_release_result(q.handle, C.byref(r)) == 0
