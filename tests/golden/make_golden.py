@@ -201,6 +201,44 @@ for i in range(12):
     th.append(dict(msg=msg.hex(), hash=tagged_hash(b"BIP0352/SharedSecret", msg).hex()))
 out["tagged_hash"] = th
 
+# ---- 7. the BIP-352 receive loop for k = 0..4 (match details), through the verifier's own primitives
+# (scripts/verify_bip352_test_vector.py:25-90 point_multiply / point_add / compress_point / tagged_hash): per transaction
+# the chain t_k = hash(ser(S) || ser32(k)), P_k = t_k*G + B_spend, the label sums P_k + L_i, their 64-bit prefixes, and an
+# outputs list a sender paying this recipient n_pay times (some through labels) would produce, shuffled among foreign
+# outputs, with the records the receiver must find: (k, output_index, label_index | -1, t_k).
+rng = random.Random(3520)
+recv = []
+for i in range(20):
+    sk = rng.randrange(1, n)
+    tweak = curve.get_xy(curve.multiply_jacobian(curve.to_jacobian(G), rng.randrange(1, n)))
+    spend = curve.get_xy(curve.multiply_jacobian(curve.to_jacobian(G), rng.randrange(1, n)))
+    L = [0, 1, 2, 3, 5][i % 5]
+    labels = [curve.get_xy(curve.multiply_jacobian(curve.to_jacobian(G), rng.randrange(1, n))) for _ in range(L)]
+    S = point_multiply(sk, tweak)
+    chain = []
+    for k in range(5):
+        ser = compress_point(S[0], S[1]) + k.to_bytes(4, "big")
+        t = int.from_bytes(tagged_hash(b"BIP0352/SharedSecret", ser), "big")
+        assert 0 < t < n
+        Pk = point_add(point_multiply(t, G), spend)
+        sums = [point_add(Pk, Lb) for Lb in labels]
+        chain.append(dict(k=k, msg=ser.hex(), t=h(t), P=[h(Pk[0]), h(Pk[1])], label_sums=[[h(q[0]), h(q[1])] for q in sums],
+                          cands=[upper64_signed(Pk[0])] + [upper64_signed(q[0]) for q in sums]))
+    n_pay = 1 + i % 5                                     # the sender pays k = 0 .. n_pay-1
+    pays = []                                             # (k, label index or -1)
+    for k in range(n_pay):
+        pays.append((k, rng.randrange(L) if L and rng.random() < 0.5 else -1))
+    outs = [chain[k]["cands"][1 + li] for k, li in pays] + [rng.randrange(-(1 << 63), 1 << 63) for _ in range(rng.randrange(0, 4))]
+    order = list(range(len(outs)))
+    rng.shuffle(order)
+    outputs = [outs[j] for j in order]
+    where = {j: pos for pos, j in enumerate(order)}
+    records = [dict(k=k, output_index=where[idx], label_index=li, t=chain[k]["t"]) for idx, (k, li) in enumerate(pays)]
+    recv.append(dict(sk=h(sk), tweak=[h(tweak[0]), h(tweak[1])], spend=[h(spend[0]), h(spend[1])],
+                     labels=[[h(l[0]), h(l[1])] for l in labels], S=[h(S[0]), h(S[1])], chain=chain, outputs=outputs,
+                     records=records))
+out["receive_loop"] = recv
+
 with open(os.path.join(HERE, "golden.json"), "w") as f:
     json.dump(out, f, indent=1)
 print("wrote", os.path.join(HERE, "golden.json"), os.path.getsize(os.path.join(HERE, "golden.json")), "bytes")

@@ -153,3 +153,23 @@ def test_streaming_details_overflow_is_flagged_not_lost(M):
         assert L.cudasp_submit_slot(q.handle, C.byref(s), 0, 0, 8) == 0
         assert L.cudasp_wait(q.handle, C.byref(r)) == 1 and r.flags == 0
         assert L.cudasp_release_result(q.handle, C.byref(r)) == 0
+
+
+def test_details_against_reference_generated_chain(M, golden):
+    """Pins K8 for k > 0: golden.json "receive_loop" holds, for 20 transactions, t_k / P_k / P_k + L_i for k = 0..4 computed with
+    the REFERENCE's own point_multiply / point_add / compress_point / tagged_hash (tests/golden/make_golden.py section 7) and
+    the records a receiver must find in an outputs list paying it 1..5 times.  One query per transaction (own keys)."""
+    for tx in golden["receive_loop"]:
+        sk = int(tx["sk"], 16).to_bytes(32, "little")
+        enc = lambda xy: R.encode_point((int(xy[0], 16), int(xy[1], 16)))      # noqa: E731
+        tweak = np.frombuffer(enc(tx["tweak"]), np.uint8).reshape(1, 64)
+        outputs = np.array(tx["outputs"], np.int64)
+        offsets = np.array([0, len(outputs)], np.uint32)
+        with M.Query(sk, enc(tx["spend"]), [enc(l) for l in tx["labels"]], batch_rows=16) as q:
+            # the candidates of k = 0 are the default path's
+            assert q.candidates(tweak)[0].tolist() == tx["chain"][0]["cands"]
+            q.enable_details()
+            ids, recs = q.scan_batch_details(tweak, outputs, offsets)
+        want = [(0, r["k"], r["output_index"], r["label_index"], int(r["t"], 16)) for r in tx["records"]]
+        assert ids.tolist() == ([0] if any(r["k"] == 0 for r in tx["records"]) else [])
+        assert recs == want

@@ -310,3 +310,13 @@ def test_details_row_follows_bip352_k_loop():
     # range check of t_k
     assert H.tweak_in_range(1) and H.tweak_in_range(R.N - 1)
     assert not H.tweak_in_range(0) and not H.tweak_in_range(R.N) and not H.tweak_in_range(2**256 - 1)
+
+
+def test_details_row_against_reference_generated_chain(golden):
+    """The K8 body on the CPU against golden.json "receive_loop": t_k for k = 0..4 and the found records come from the
+    reference's own primitives (tests/golden/make_golden.py section 7), not from this repo's restatement."""
+    for tx in golden["receive_loop"]:
+        enc = lambda xy: R.encode_point((int(xy[0], 16), int(xy[1], 16)))      # noqa: E731
+        sk = int(tx["sk"], 16).to_bytes(32, "little")
+        got = H.details_row(sk, enc(tx["spend"]), [enc(l) for l in tx["labels"]], enc(tx["S"]), tx["outputs"])
+        assert got == [(r["k"], r["output_index"], r["label_index"], int(r["t"], 16)) for r in tx["records"]]

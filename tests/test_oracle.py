@@ -149,3 +149,26 @@ def test_edge_semantics():
     z = R.row_intermediates(0, R.parse_point(tw), R.G)
     assert z["msg"] == b"\x02" + b"\x00" * 36
     assert CO.row(R.encode_scalar(0), spend, [], tw)["cands"] == z["cands"]
+
+
+def test_receive_loop_golden(golden):
+    """k > 0 (match details): the oracle's receive loop against the chain t_k, P_k, P_k + L_i produced with the reference's
+    own primitives (scripts/verify_bip352_test_vector.py:25-90) for k = 0..4 -- golden.json "receive_loop"."""
+    for tx in golden["receive_loop"]:
+        sk, tw = I(tx["sk"]), (I(tx["tweak"][0]), I(tx["tweak"][1]))
+        spend = (I(tx["spend"][0]), I(tx["spend"][1]))
+        labels = [(I(l[0]), I(l[1])) for l in tx["labels"]]
+        S = R.pt_mul(sk, tw)
+        assert S == (I(tx["S"][0]), I(tx["S"][1]))
+        for c in tx["chain"]:
+            msg = bytes([0x02 + (S[1] & 1)]) + S[0].to_bytes(32, "big") + c["k"].to_bytes(4, "big")
+            assert msg.hex() == c["msg"]
+            t = int.from_bytes(R.tagged_hash(msg), "big")
+            assert t == I(c["t"])
+            Pk = R.pt_add(R.pt_mul(t, R.G), spend)
+            assert Pk == (I(c["P"][0]), I(c["P"][1]))
+            sums = [R.pt_add(Pk, L) for L in labels]
+            assert sums == [(I(q[0]), I(q[1])) for q in c["label_sums"]]
+            assert [R.upper64_signed(Pk[0])] + [R.upper64_signed(q[0]) for q in sums] == c["cands"]
+        got = R.receive_scan_row(sk, tw, spend, labels, tx["outputs"])
+        assert got == [(r["k"], r["output_index"], r["label_index"], I(r["t"])) for r in tx["records"]]
