@@ -320,6 +320,10 @@ int ensure_device(cudasp_query *q, int di) {
   int rc = get_device_gtab(q, dc.device, &dc.d_gtab);
   if (rc) return rc;
   CU(q, cudaSetDevice(dc.device));
+  if (const char *e = getenv("CUDASP_L2_FETCH")) {       // tuning aid: L2 fetch granularity (32 / 64 / 128 B) for K3's random table reads
+    const int v = atoi(e);
+    if (v == 32 || v == 64 || v == 128) CU(q, cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v));
+  }
   if (!dc.own_stream) CU(q, cudaStreamCreateWithFlags(&dc.own_stream, cudaStreamNonBlocking));
   if (q->n_labels && !dc.d_labels) {
     CU(q, cudaMalloc(&dc.d_labels, q->n_labels * sizeof(ge)));

@@ -146,8 +146,35 @@ CSP_HD void gej_dbl(gej &r, const gej &p) {
 // ---- mixed addition r = p + q (q affine), p != +-q, neither infinity:  8M + 3S
 //   Z1Z1 = Z1^2, U2 = x2*Z1Z1, S2 = y2*Z1*Z1Z1, H = U2 - X1, R = S2 - Y1,
 //   HH = H^2, HHH = H*HH, V = X1*HH, X3 = R^2 - HHH - 2V, Y3 = R*(V - X3) - Y1*HHH, Z3 = Z1*H
-// If h_out is given it receives H (so callers can test H == 0 or reuse Z ratios).
+// If h_out is given it receives Z3 / Z1 (= H here), so callers can test H == 0 or reuse Z ratios.
+// With CSP_MADD_7M4S the reference's madd-2007-bl shape (7M + 4S, gECC/scripts/ec_ops.py:292-317) is compiled instead:
+// Z3 = (Z1 + H)^2 - Z1Z1 - HH replaces the multiplication Z1*H by a squaring and three more linear combinations (measured:
+// DESIGN.md section 6 -- on this field layer a linear combination costs a quarter of what a squaring saves over a product).
 CSP_HD void gej_add_ge(gej &r, const gej &p, const fe &qx, const fe &qy, fe *h_out = nullptr) {
+#if defined(CSP_MADD_7M4S)
+  fe z1z1, u2, s2, h, rr, hh, i4, j, v, t, x3, zh;
+  fe_sqr(z1z1, p.z);
+  fe_mul(u2, qx, z1z1);
+  fe_mul(s2, qy, p.z);
+  fe_mul(s2, s2, z1z1);
+  fe_sub(h, u2, p.x);
+  fe_add(zh, p.z, h);
+  fe_lin2<2, -2>(rr, s2, p.y);
+  fe_sqr(hh, h);
+  fe_sqr(zh, zh);
+  fe_lin3<1, -1, -1>(r.z, zh, z1z1, hh);   // 2*Z1*H
+  fe_lin1<4>(i4, hh);
+  fe_mul(j, h, i4);
+  fe_mul(v, p.x, i4);
+  fe_sqr(t, rr);
+  fe_lin3<1, -1, -2>(x3, t, j, v);
+  fe_sub(t, v, x3);
+  fe_mul(t, rr, t);
+  fe_mul(u2, p.y, j);
+  fe_lin2<1, -2>(r.y, t, u2);
+  r.x = x3;
+  if (h_out) fe_lin1<2>(*h_out, h);        // callers use it as the ratio Z3 / Z1, which is 2H here
+#else
   fe z1z1, u2, s2, h, rr, hh, hhh, v, t, x3;
   fe_sqr(z1z1, p.z);
   fe_mul(u2, qx, z1z1);
@@ -167,6 +194,7 @@ CSP_HD void gej_add_ge(gej &r, const gej &p, const fe &qx, const fe &qy, fe *h_o
   fe_sub(r.y, t, u2);
   r.x = x3;
   if (h_out) *h_out = h;
+#endif
 }
 
 }  // namespace csp
