@@ -880,7 +880,15 @@ static int take_result(cudasp_query *q, cudasp_result *r, bool block) {
   {
     std::lock_guard<std::mutex> lk(q->mu);
     if (q->inflight.empty()) return 0;
-    for (auto it = q->inflight.begin(); it != q->inflight.end(); ++it) {
+    // per device only the OLDEST batch is asked (batches of one device finish roughly in submit order): at most one
+    // event query per device under the lock, however many batches are in flight
+    uint64_t seen_devices = 0;
+    size_t n_seen = 0;
+    for (auto it = q->inflight.begin(); it != q->inflight.end() && n_seen < q->devs.size(); ++it) {
+      const uint64_t bit = 1ull << ((*it)->dev_index & 63);
+      if (seen_devices & bit) continue;
+      seen_devices |= bit;
+      n_seen++;
       const cudaError_t e = cudaEventQuery((*it)->done);
       if (e == cudaErrorNotReady) continue;
       if (e != cudaSuccess) return fail_locked(q, CUDASP_ERR_CUDA, cudaGetErrorString(e));

@@ -32,6 +32,7 @@ namespace {
 
 constexpr idx_t SCALAR_SIZE = 32;      // scan_private_key: 32 B little-endian
 constexpr idx_t POINT_SIZE = 64;       // x_LE || y_LE
+constexpr idx_t TXID_SIZE = 32;        // the usual txid length (any length is accepted)
 constexpr idx_t SEC1_SIZE = 33;        // (02|03) || x_BE: the index's own storage format, decompressed on the GPU
 constexpr idx_t DEFAULT_BATCH = 300000;  // reference default (:473)
 constexpr idx_t MAX_BATCH = 10000000;
@@ -46,11 +47,79 @@ struct CudaspScanBindData : public TableFunctionData {
 	bool details = false;  // details := true (extension): one result row per found output, + k, output_index, label_index, t_k
 };
 
+// Growable byte buffer that does NOT value-initialise what it grows by (vector::resize would write every txid byte twice)
+// and keeps its capacity when a batch's metadata is recycled.
+template <class T>
+struct RawBuffer {
+	T *ptr = nullptr;
+	size_t len = 0, cap = 0;
+	RawBuffer() = default;
+	RawBuffer(const RawBuffer &) = delete;
+	RawBuffer &operator=(const RawBuffer &) = delete;
+	~RawBuffer() {
+		free(ptr);
+	}
+	void Reserve(size_t n) {
+		if (n > cap) {
+			const size_t want = MaxValue<size_t>(n, cap + cap / 2);
+			T *p = static_cast<T *>(realloc(ptr, want * sizeof(T)));
+			if (!p) {
+				throw std::bad_alloc();
+			}
+			ptr = p;
+			cap = want;
+		}
+	}
+	// make room for n more elements and return where they go
+	T *Grow(size_t n) {
+		Reserve(len + n);
+		T *at = ptr + len;
+		len += n;
+		return at;
+	}
+	void Truncate(size_t n) {
+		len = n;
+	}
+};
+
 // Host-side columns of one submitted batch that never go to the GPU: only needed for matched rows.
 struct InFlightBatch {
-	vector<char> txid_bytes;
-	vector<uint32_t> txid_end;   // txid i = txid_bytes[txid_end[i-1] .. txid_end[i])
-	vector<int32_t> heights;
+	// txid i = txid_bytes[txid_end[i-1] .. txid_end[i]); while every txid so far is TXID_SIZE bytes (the normal case) the
+	// index is implicit (txid i at TXID_SIZE * i) and txid_end stays empty
+	RawBuffer<char> txid_bytes;
+	vector<uint32_t> txid_end;
+	bool txid_fixed = true;
+	RawBuffer<int32_t> heights;
+	uint32_t rows = 0;
+
+	void Clear() {
+		txid_bytes.Truncate(0);
+		txid_end.clear();
+		heights.Truncate(0);
+		txid_fixed = true;
+		rows = 0;
+	}
+	// leave the implicit index: write the explicit one for the rows added so far
+	void MakeTxidIndexExplicit(idx_t txid_size) {
+		if (!txid_fixed) {
+			return;
+		}
+		txid_fixed = false;
+		txid_end.resize(rows);
+		for (uint32_t i = 0; i < rows; i++) {
+			txid_end[i] = (uint32_t)((i + 1) * txid_size);
+		}
+	}
+	void AddTxid(const string_t &tx, idx_t txid_size) {
+		const idx_t n = tx.GetSize();
+		if (txid_fixed && n != txid_size) {
+			MakeTxidIndexExplicit(txid_size);
+		}
+		memcpy(txid_bytes.Grow(n), tx.GetData(), n);
+		if (!txid_fixed) {
+			txid_end.push_back((uint32_t)txid_bytes.len);
+		}
+	}
 	const uint8_t *tweak_keys = nullptr;  // the slot's pinned buffer: valid until the result is released
 	uint32_t key_bytes = 64;              // one key format per batch (CUDASP_KEYS_XY64 / CUDASP_KEYS_SEC1_33)
 };
@@ -102,6 +171,8 @@ struct CudaspScanLocalState : public LocalTableFunctionState {
 	bool input_consumed = false;  // emit_early: the current input chunk is already staged (we are being re-called for output)
 	double accumulate_s = 0, first_input = 0;
 	uint64_t rows_seen = 0, batches = 0;
+	uint32_t chunks_since_poll = 0;
+	uint64_t rows_fast = 0;  // rows staged by AccumulateInput's column-wise fast path (trace)
 	cudasp_slot slot;
 	uint32_t rows = 0;
 	uint64_t n_outputs = 0;
@@ -302,9 +373,10 @@ static void CollectResult(CudaspScanState &state, const cudasp_result &r) {
 		std::lock_guard<std::mutex> guard(state.output_lock);
 		for (uint32_t k = 0; k < n_rows_out; k++) {
 			const uint32_t i = state.details ? det[k].row : r.match_ids[k];
-			const uint32_t b = i ? meta->txid_end[i - 1] : 0, e = meta->txid_end[i];
-			state.output_txids.emplace_back(meta->txid_bytes.data() + b, e - b);
-			state.output_heights.push_back(meta->heights[i]);
+			const uint32_t b = meta->txid_fixed ? (uint32_t)(i * TXID_SIZE) : (i ? meta->txid_end[i - 1] : 0);
+			const uint32_t e = meta->txid_fixed ? (uint32_t)((i + 1) * TXID_SIZE) : meta->txid_end[i];
+			state.output_txids.emplace_back(meta->txid_bytes.ptr + b, e - b);
+			state.output_heights.push_back(meta->heights.ptr[i]);
 			state.output_tweak_keys.emplace_back(const_char_ptr_cast(meta->tweak_keys) + (size_t)i * meta->key_bytes, meta->key_bytes);
 			if (state.details) {
 				state.output_details.push_back(det[k]);
@@ -314,9 +386,7 @@ static void CollectResult(CudaspScanState &state, const cudasp_result &r) {
 	if (cudasp_release_result(state.query, &r) != CUDASP_OK) {
 		ThrowGpu(state, "cudasp_release_result");
 	}
-	meta->txid_bytes.clear();
-	meta->txid_end.clear();
-	meta->heights.clear();
+	meta->Clear();
 	std::lock_guard<std::mutex> guard(state.inflight_lock);
 	state.meta_pool.push_back(std::move(meta));
 }
@@ -380,9 +450,8 @@ static void EnsureSlot(CudaspScanState &state, CudaspScanLocalState &local) {
 	}
 	const uint32_t round = state.batches_started++ / state.n_devices;
 	local.batch_limit = MaxValue<uint32_t>(MinValue<uint32_t>(state.steady_limit, 16384u), state.steady_limit >> (round < 3 ? 3 - round : 0));
-	local.meta->txid_bytes.reserve((size_t)local.batch_limit * 32);
-	local.meta->txid_end.reserve(local.batch_limit);
-	local.meta->heights.reserve(local.batch_limit);
+	local.meta->txid_bytes.Reserve((size_t)local.batch_limit * TXID_SIZE);
+	local.meta->heights.Reserve(local.batch_limit);
 	local.meta->tweak_keys = local.slot.tweak_keys;
 }
 
@@ -437,7 +506,131 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 	auto lists = UnifiedVectorFormat::GetData<list_entry_t>(list_f);
 	auto values = UnifiedVectorFormat::GetData<int64_t>(child_f);
 
-	for (idx_t r = 0; r < count; r++) {
+	// Fast path (what a Parquet or table scan delivers): no NULL in this chunk and the lists of consecutive rows adjacent in
+	// the child vector.  Rows are then staged column by column for as many rows as fit the batch: one fixed-size copy per
+	// key and per txid, one pass over the heights, ONE copy for the outputs of the whole run.  Dictionary-encoded Parquet
+	// pages arrive as dictionary vectors (a selection vector over the dictionary, and a validity mask that exists even
+	// when every entry is valid), so txid / height / tweak_key are read through their selection vectors and "no NULL" is
+	// established by looking at the rows, not at the mask pointer.  Any row that breaks the pattern (other key length, a
+	// gap between lists, outputs that overflow the slot) ends the run; the general row-by-row loop below takes over from
+	// there for the rest of the chunk.
+	auto all_rows_valid = [count](const UnifiedVectorFormat &f) {
+		if (f.validity.AllValid()) {
+			return true;
+		}
+		for (idx_t i = 0; i < count; i++) {
+			if (!f.validity.RowIsValid(f.sel->get_index(i))) {
+				return false;
+			}
+		}
+		return true;
+	};
+	idx_t r = 0;
+	const bool flat = !list_f.sel->IsSet() && !child_f.sel->IsSet() && list_f.validity.AllValid() && child_f.validity.AllValid() &&
+	                  all_rows_valid(txid_f) && all_rows_valid(height_f) && all_rows_valid(tweak_f);
+	const sel_t *tsel = txid_f.sel->IsSet() ? txid_f.sel->data() : nullptr;
+	const sel_t *hsel = height_f.sel->IsSet() ? height_f.sel->data() : nullptr;
+	const sel_t *wsel = tweak_f.sel->IsSet() ? tweak_f.sel->data() : nullptr;
+#define CUDASP_AT(sel, i) ((sel) ? (idx_t)(sel)[i] : (idx_t)(i))
+	while (flat && r < count) {
+		const idx_t key_size = tweaks[CUDASP_AT(wsel, r)].GetSize();
+		if (key_size != POINT_SIZE && key_size != SEC1_SIZE) {
+			break;
+		}
+		if (local.have_slot && local.rows && local.key_bytes != key_size) {
+			SubmitSlot(state, local);
+		}
+		EnsureSlot(state, local);
+		if (local.rows == 0) {
+			local.key_bytes = local.meta->key_bytes = (uint32_t)key_size;
+		}
+		const uint32_t row0 = local.rows;
+		idx_t n = MinValue<idx_t>(count - r, MinValue<uint32_t>(local.batch_limit, local.slot.cap_rows) - row0);
+		// lists: adjacent, and fitting the slot's output capacity
+		const idx_t first_off = lists[r].offset;
+		uint64_t acc = 0;
+		uint32_t *offs = local.slot.out_offsets + row0 + 1;
+		const uint64_t room = local.slot.cap_outputs - local.n_outputs;
+		idx_t m = 0;
+		for (; m < n; m++) {
+			const list_entry_t &le = lists[r + m];
+			if (le.offset != first_off + acc || acc + le.length > room) {
+				break;
+			}
+			acc += le.length;
+			offs[m] = (uint32_t)(local.n_outputs + acc);
+		}
+		n = m;
+		// keys: one length for the run
+		uint8_t *kdst = local.slot.tweak_keys + (size_t)row0 * key_size;
+		if (key_size == POINT_SIZE) {
+			for (m = 0; m < n; m++) {
+				const string_t &tw = tweaks[CUDASP_AT(wsel, r + m)];
+				if (tw.GetSize() != POINT_SIZE) {
+					break;
+				}
+				memcpy(kdst + m * POINT_SIZE, tw.GetData(), POINT_SIZE);
+			}
+		} else {
+			for (m = 0; m < n; m++) {
+				const string_t &tw = tweaks[CUDASP_AT(wsel, r + m)];
+				if (tw.GetSize() != SEC1_SIZE) {
+					break;
+				}
+				memcpy(kdst + m * SEC1_SIZE, tw.GetData(), SEC1_SIZE);
+			}
+		}
+		n = m;
+		if (n == 0) {
+			break;  // the row at r does not fit this pattern (e.g. its outputs overflow an empty slot): general path
+		}
+		const uint64_t n_out = (uint64_t)offs[n - 1] - local.n_outputs;
+		if (n_out) {
+			memcpy(local.slot.outputs + local.n_outputs, values + first_off, n_out * sizeof(int64_t));
+		}
+		auto &meta = *local.meta;
+		int32_t *hdst = meta.heights.Grow(n);
+		if (hsel) {
+			for (m = 0; m < n; m++) {
+				hdst[m] = heights[hsel[r + m]];
+			}
+		} else {
+			memcpy(hdst, heights + r, n * sizeof(int32_t));
+		}
+		if (meta.txid_fixed) {
+			char *tdst = meta.txid_bytes.Grow(n * TXID_SIZE);
+			for (m = 0; m < n; m++) {
+				const string_t &tx = txids[CUDASP_AT(tsel, r + m)];
+				if (tx.GetSize() != TXID_SIZE) {
+					break;
+				}
+				memcpy(tdst + m * TXID_SIZE, tx.GetData(), TXID_SIZE);
+			}
+			if (m < n) {  // an odd-sized txid: switch this batch to the explicit index and append the rest one by one
+				meta.txid_bytes.Truncate((size_t)(row0 + m) * TXID_SIZE);
+				meta.rows = (uint32_t)(row0 + m);
+				for (; m < n; m++) {
+					meta.AddTxid(txids[CUDASP_AT(tsel, r + m)], TXID_SIZE);
+					meta.rows++;
+				}
+			}
+		} else {
+			for (m = 0; m < n; m++) {
+				meta.AddTxid(txids[CUDASP_AT(tsel, r + m)], TXID_SIZE);
+			}
+		}
+		meta.rows = (uint32_t)(row0 + n);
+		local.n_outputs += n_out;
+		local.rows = (uint32_t)(row0 + n);
+		local.rows_fast += n;
+		r += n;
+		if (local.rows >= local.batch_limit || local.rows >= local.slot.cap_rows) {
+			SubmitSlot(state, local);
+		}
+	}
+#undef CUDASP_AT
+
+	for (; r < count; r++) {
 		const idx_t ti = txid_f.sel->get_index(r), hi = height_f.sel->get_index(r), wi = tweak_f.sel->get_index(r);
 		if (!txid_f.validity.RowIsValid(ti) || !height_f.validity.RowIsValid(hi) || !tweak_f.validity.RowIsValid(wi)) {
 			continue;
@@ -481,10 +674,9 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 		local.n_outputs = n_out;
 		local.slot.out_offsets[row + 1] = (uint32_t)n_out;
 		auto &meta = *local.meta;
-		const string_t &tx = txids[ti];
-		meta.txid_bytes.insert(meta.txid_bytes.end(), tx.GetData(), tx.GetData() + tx.GetSize());
-		meta.txid_end.push_back((uint32_t)meta.txid_bytes.size());
-		meta.heights.push_back(heights[hi]);
+		meta.AddTxid(txids[ti], TXID_SIZE);
+		*meta.heights.Grow(1) = heights[hi];
+		meta.rows = row + 1;
 		local.rows = row + 1;
 		if (local.rows >= local.batch_limit || local.rows >= local.slot.cap_rows) {
 			SubmitSlot(state, local);
@@ -540,7 +732,12 @@ static OperatorResultType CudaspScanFunction(ExecutionContext &context, TableFun
 			local.first_input = t0;
 		}
 		AccumulateInput(state, local, bind, input);
-		Drain(state, false);
+		// Finished batches are collected when a worker needs a slot (EnsureSlot) and at the end (Final).  Polling after
+		// every 2 048-row chunk from every worker only contends for the query's lock; with emit_early it is what
+		// brings the matches out early, so it stays there (every fourth chunk of a worker).
+		if (bind.emit_early && (++local.chunks_since_poll & 3) == 0) {
+			Drain(state, false);
+		}
 		if (TraceOn()) {
 			local.accumulate_s += NowSec() - t0;
 			local.rows_seen += input.size();
@@ -569,8 +766,9 @@ static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &cont
 
 	if (!local.finalized) {
 		if (TraceOn()) {
-			fprintf(stderr, "[cudasp] worker: %llu rows, accumulate+drain %.3f s, span %.3f s\n",
-			        (unsigned long long)local.rows_seen, local.accumulate_s, local.rows_seen ? NowSec() - local.first_input : 0.0);
+			fprintf(stderr, "[cudasp] worker: %llu rows (%llu column-wise), accumulate+drain %.3f s, span %.3f s\n",
+			        (unsigned long long)local.rows_seen, (unsigned long long)local.rows_fast, local.accumulate_s,
+			        local.rows_seen ? NowSec() - local.first_input : 0.0);
 		}
 		SubmitSlot(state, local);
 		Drain(state, false);

@@ -144,7 +144,7 @@ def test_streaming_details_overflow_is_flagged_not_lost(M):
         r = B.Result()
         assert L.cudasp_wait(q.handle, C.byref(r)) == 1
         assert r.tag == 7 and r.flags & 1
-        assert [r.match_ids[i] for i in range(r.n_matches)] == T["expected"].tolist()
+        assert [r.match_ids[i] for i in range(r.n_matches)] == sorted(want)      # the matches are complete
         d, n = C.POINTER(B.MatchDetail)(), C.c_uint32(0)
         assert L.cudasp_result_details(q.handle, C.byref(r), C.byref(d), C.byref(n)) == 0
         assert n.value == 8
