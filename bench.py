@@ -13,8 +13,15 @@ data path).  A "step" is one pass of the whole table through the hot path.
   roofline  integer-multiply bound: achieved IMAD32 lane-ops/s of the dominant kernel
          (k_ladder) = rows * 168786 / its CUDA-event time, against the IMAD32 peak measured by
          tools/imad_peak on this box (fallback: profiles/r01n_imad_peak.json)
-  cpu_baseline  the oracle's C port of the reference algorithm on the host cores, bounded sample
+  cpu_baseline  the oracle's C port of the reference algorithm on the host cores, bounded sample (the fastest correct CPU scan
+         in the repo); cpu_openssl = baseline/cpu_scan_openssl.cpp (OpenSSL 3 EC_POINT_mul, BASELINE.md B-cpu) beside it
   python_baseline  the reference's own CPU code for the path is a pure-Python verifier: oracle/ref_scan.py, 1 core, ~4 s
+  one_handle (N > 1, rank 0 alone after the ranks' timed region)  ONE query handle over all N devices, ONE host table of
+         N x rows rows, staged by several host threads through the C ABI -- the in-process form of the reference's
+         thread->GPU round-robin (src/cudasp_extension.cu:516-532), the case its README names as its scaling wall
+  duckdb  the same through the real DuckDB engine + the `cudasp` extension from a Parquet file (duckdb_ext/bin/duckdb):
+         N = 1: 10 M rows with the bench's label count; N > 1: config C5's shape (12.5 M rows per GPU, 16 label keys,
+         multi-output rows; 100 M rows at N = 8), all GPUs of the box in one SQL query
 """
 import argparse
 import json
@@ -59,6 +66,9 @@ def parse():
     ap.add_argument("--labels", type=int, default=1)
     ap.add_argument("--batch", type=int, default=300000)
     ap.add_argument("--streams", type=int, default=2)
+    ap.add_argument("--host-threads", type=int, default=0, help="staging threads of the e2e call (0 = the library's choice)")
+    ap.add_argument("--no-legs", action="store_true", help="skip the one_handle and duckdb legs (quick runs)")
+    ap.add_argument("--duckdb-rows", type=int, default=0, help="rows of the duckdb leg's Parquet file (0 = 10 M at N = 1, 12.5 M per GPU at N > 1)")
     return ap.parse_args()
 
 
@@ -94,14 +104,24 @@ class ClockSampler(threading.Thread):
 
 
 def measured_imad_peak():
-    """IMAD32 lane-ops/s: run tools/imad_peak on this GPU if the binary travelled, else the committed profile."""
+    """(IMAD32 lane-ops/s, source, IMAD.WIDE products/s): tools/imad_peak on this GPU if the binary travelled, else the committed profile."""
     exe = os.path.join(ROOT, "tools", "imad_peak")
     try:
-        out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
-        return float(json.loads(out)["imad_lo"]["lane_ops_per_s"]), "measured live by tools/imad_peak (mad.lo.u32)"
+        j = json.loads(subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout)
+        src = "measured live by tools/imad_peak (mad.lo.u32; wide: 64-bit multiply-add, distinct operands)"
     except Exception:
         with open(os.path.join(ROOT, "profiles", "r01n_imad_peak.json")) as f:
-            return float(json.load(f)["imad_lo"]["lane_ops_per_s"]), "profiles/r01n_imad_peak.json (tools/imad_peak, earlier call)"
+            j = json.load(f)
+        src = "profiles/r01n_imad_peak.json (tools/imad_peak, earlier call)"
+    return float(j["imad_lo"]["lane_ops_per_s"]), src, float(j["imad_wide_distinct_operands"]["lane_ops_per_s"])
+
+
+# 64-bit multiply-adds (IMAD.WIDE) K1 EXECUTES per row: 73 per multiplication (64 + 9 fold), 44 per squaring (36 + 8), so
+# 3M + 4S = 395 per doubling, 8M + 3S = 716 per mixed addition, 4 106 for the odd-multiples table and the final Z scale
+# (rowfn.cuh ladder_row); the op counts are the query's own (cudasp_query_info).  ncu's count for the C3 key: 86 988
+# (profiles/traffic.json, profiles/r02a_ncu_summary.md).
+def ladder_wide_per_row(info):
+    return 4106 + 395 * info["ladder_dbl"] + 716 * info["ladder_add"]
 
 
 def cpu_sample(T, rows_sample, threads):
@@ -193,6 +213,115 @@ def reference_arm(args, config, cores, synth):
     return base
 
 
+def cpu_openssl_sample(T, rows_sample, threads):
+    """baseline B-cpu: OpenSSL 3 EC_POINT_mul / EC_POINT_add / SHA256, all host cores, bounded sample."""
+    try:
+        from baseline import cpu_scan
+        if not cpu_scan.available():
+            return {"unavailable": "OpenSSL development files not present"}
+        n = min(rows_sample, T["tweaks"].shape[0])
+        t0 = time.perf_counter()
+        flags, _ = cpu_scan.scan(T["sk"], T["spend"], T["labels"], T["tweaks"][:n], T["outputs"], T["offsets"][: n + 1], threads=threads)
+        dt = time.perf_counter() - t0
+        ok = bool(np.array_equal(np.nonzero(flags)[0].astype(np.uint32), T["expected"][T["expected"] < n]))
+        return {"value": n / dt, "unit": "rows/s", "cores": threads, "rows_per_s_per_core": n / dt / threads, "kind": "port",
+                "library": "OpenSSL 3 (EC_POINT_mul, EC_POINT_add, SHA256) -- baseline/cpu_scan_openssl.cpp", "flags_equal_planted": ok,
+                "sample": "%d rows of the same table, %d threads, %.1f s" % (n, threads, dt)}
+    except Exception as ex:      # noqa: BLE001  (the baseline is optional; the product line must still print)
+        return {"unavailable": repr(ex)[:200]}
+
+
+def one_handle_leg(M, T, rows, n_dev, batch, steps):
+    """ONE query handle over n_dev devices, ONE host table of n_dev x rows rows (rank 0's table repeated), several host staging
+    threads through cudasp_scan_batch_mt.  Rank 0 alone; the other ranks have left."""
+    cores = os.cpu_count() or 1
+    threads = max(2, min(4 * n_dev, cores // 2))
+    tw = np.tile(T["tweaks"], (n_dev, 1))
+    outs = np.tile(T["outputs"], n_dev)
+    n_out = int(T["offsets"][-1])
+    off = np.concatenate([T["offsets"][:-1].astype(np.uint64) + np.uint64(k * n_out) for k in range(n_dev)] + [np.array([n_dev * n_out], np.uint64)])
+    assert int(off[-1]) < 2 ** 32
+    off = off.astype(np.uint32)
+    expected = np.concatenate([T["expected"].astype(np.uint64) + np.uint64(k * rows) for k in range(n_dev)]).astype(np.uint32)
+    q = M.Query(T["sk"], T["spend"], T["labels"], devices=list(range(n_dev)), batch_rows=batch, max_outputs_per_batch=17 * batch)
+    try:
+        ok = True
+        for _ in range(2):
+            ok &= bool(np.array_equal(q.scan_batch(tw, outs, off, host_threads=threads), expected))
+        h0, d0 = q.transfer_bytes()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            ids = q.scan_batch(tw, outs, off, host_threads=threads)
+        dt = (time.perf_counter() - t0) / steps
+        ok &= bool(np.array_equal(ids, expected))
+        h1, d1 = q.transfer_bytes()
+        return {"value": n_dev * rows / dt, "unit": "rows/s", "ms_per_step": 1e3 * dt, "rows": n_dev * rows, "devices": n_dev,
+                "host_threads": threads, "host_cores": cores, "steps": steps, "match_set_ok": ok,
+                "h2d_bytes_per_step": (h1 - h0) // steps, "d2h_bytes_per_step": (d1 - d0) // steps,
+                "api": "one cudasp_query over %d devices, cudasp_scan_batch_mt from ONE host table, %d staging threads" % (n_dev, threads)}
+    finally:
+        q.close()
+
+
+def duckdb_leg(synth, rows_file, replicate, labels, geom_p, batch, n_dev):
+    """SELECT count(*) FROM cudasp_scan((SELECT ... FROM read_parquet(...)), ...) through duckdb_ext/bin/duckdb: all visible GPUs in
+    one query, Parquet decode + AccumulateInput + staging + kernels + result inside the timed query.  The file is read `replicate`
+    times by the one query (config C5: 100 M rows, 16 label keys, multi-output rows on 8 GPUs)."""
+    exe = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "duckdb_ext", "bin", "duckdb")
+    if not os.path.exists(exe):
+        return {"unavailable": "duckdb_ext/bin/duckdb not built (tools/build_duckdb.sh needs the vendored DuckDB source)"}
+    import tempfile
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    t0 = time.perf_counter()
+    seed = 352005 if labels == 16 else 352003
+    T = synth.make_table(rows_file, seed, n_labels=labels, n_base=1000 if labels == 16 else 100, n_per_label=100 if labels else 0,
+                         batch_rows=batch, geom_p=geom_p, max_extra=63 if geom_p < 0.5 else 15)
+    off = T["offsets"].astype(np.int64)
+    tw = pa.FixedSizeBinaryArray.from_buffers(pa.binary(64), rows_file, [None, pa.py_buffer(T["tweaks"].tobytes())]).cast(pa.binary())
+    txid = np.zeros((rows_file, 32), np.uint8)
+    txid[:, :8] = np.arange(rows_file, dtype=np.uint64).view(np.uint8).reshape(rows_file, 8)
+    tx = pa.FixedSizeBinaryArray.from_buffers(pa.binary(32), rows_file, [None, pa.py_buffer(txid.tobytes())]).cast(pa.binary())
+    outs = pa.ListArray.from_arrays(pa.array(off.astype(np.int32), pa.int32()), pa.array(T["outputs"], pa.int64()))
+    tbl = pa.table({"txid": tx, "height": pa.array((800000 + np.arange(rows_file) // 3000).astype(np.int32)), "tweak_key": tw, "outputs": outs})
+    d = tempfile.mkdtemp(prefix="cudasp_bench_")
+    path = os.path.join(d, "t.parquet")
+    pq.write_table(tbl, path, row_group_size=122880, compression="NONE")
+    del tbl, tw, tx, outs, txid
+    gen_s = time.perf_counter() - t0
+
+    def blob(b):
+        return "'" + "".join("\\x%02x" % c for c in b) + "'::BLOB"
+    lab = "[" + ", ".join(blob(l) for l in T["labels"]) + "]" + ("" if T["labels"] else "::BLOB[]")
+    src = "read_parquet([%s])" % ", ".join(["'%s'" % path] * replicate)
+    threads = os.cpu_count() or 1
+    scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM %s), %s, %s, %s, batch_size := %d);" % (
+        src, blob(T["sk"]), blob(T["spend"]), lab, batch)
+    plain = "SELECT count(*), sum(height), sum(octet_length(tweak_key)), sum(octet_length(txid)), sum(list_sum(outputs)) FROM %s;" % src
+    sql = "PRAGMA threads=%d;\n.timer on\n%s\n%s\n%s\n%s\n" % (threads, scan, scan, scan, plain)
+    try:
+        p = subprocess.run([exe, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1200)
+        lines = [l for l in p.stdout.strip().splitlines() if l]
+        times = [float(l.split("real")[1].split()[0]) for l in lines if l.startswith("Run Time")]
+        vals = [l for l in lines if not l.startswith("Run Time")]
+        want = len(T["expected"]) * replicate
+        ok = p.returncode == 0 and len(vals) >= 3 and all(int(v) == want for v in vals[:3]) and len(times) >= 4
+        if not ok:
+            return {"unavailable": "duckdb query failed: rc %d, %s" % (p.returncode, (p.stderr or p.stdout)[-300:])}
+        warm = min(times[1:3])
+        rows = rows_file * replicate
+        return {"value": rows / warm, "unit": "rows/s", "rows": rows, "labels": labels, "mean_outputs_per_row": float(len(T["outputs"])) / rows_file,
+                "devices": n_dev, "duckdb_threads": threads, "scan_s_warm": warm, "scan_s_first": times[0], "plain_read_all_columns_s": times[3],
+                "matches_expected": want, "match_count_ok": True, "file_rows": rows_file, "read_times": replicate, "table_gen_s": round(gen_s, 1),
+                "query": "SELECT count(*) FROM cudasp_scan((SELECT txid,height,tweak_key,outputs FROM read_parquet(...)), sk, spend, labels, batch_size := %d)" % batch}
+    finally:
+        try:
+            os.remove(path)
+            os.rmdir(d)
+        except OSError:
+            pass
+
+
 _REAL_STDOUT = None
 
 
@@ -244,6 +373,8 @@ def main():
     import torch
     import cudasp_b200_loader
     M = cudasp_b200_loader.load()
+    from importlib import import_module
+    S = import_module("cudasp_b200.host.sharding")      # batch ranges, CSR rebasing, max-over-ranks (the N > 1 host logic)
     if not torch.cuda.is_available() or M.lib().cudasp_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path")
     dist = None
@@ -261,11 +392,10 @@ def main():
     batches = []
     d_tw = torch.from_numpy(T["tweaks"]).cuda()
     d_out = torch.from_numpy(T["outputs"]).cuda()
-    for base in range(0, rows, args.batch):
-        cnt = min(args.batch, rows - base)
-        o0 = int(T["offsets"][base])
-        off = (T["offsets"][base: base + cnt + 1] - o0).astype(np.int64)
-        batches.append(dict(base=base, cnt=cnt, tw=d_tw[base: base + cnt], out=d_out[o0:], off=torch.from_numpy(off).to(torch.int32).cuda(),
+    for base, end in S.batch_ranges(0, rows, args.batch):
+        cnt = end - base
+        off, o0, _ = S.local_csr(T["offsets"], base, end)
+        batches.append(dict(base=base, cnt=cnt, tw=d_tw[base: base + cnt], out=d_out[o0:], off=torch.from_numpy(off.astype(np.int64)).to(torch.int32).cuda(),
                             ids=torch.zeros(cnt, dtype=torch.int32, device="cuda"), n=torch.zeros(1, dtype=torch.int32, device="cuda")))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     main_s = torch.cuda.current_stream()
@@ -289,11 +419,7 @@ def main():
         return start, end
 
     def gathered_ids():
-        out = []
-        for b in batches:
-            n = int(b["n"].item())
-            out.extend((b["ids"][:n].to(torch.int64) + b["base"]).tolist())
-        return np.array(sorted(out), dtype=np.uint32)
+        return S.merge_matches([(b["base"], b["ids"][: int(b["n"].item())].cpu().numpy().astype(np.uint32)) for b in batches])
 
     def barrier():
         torch.cuda.synchronize()
@@ -316,26 +442,22 @@ def main():
     dev_ms = sum(s.elapsed_time(e) for s, e in evs) / args.steps
     launches = q.launch_count() - launches0
 
-    # e2e: public host API, host buffers, copies inside the timed region
-    sms = torch.cuda.get_device_properties(dev).multi_processor_count
-    piece = min(args.batch, sms * 4 * 128 * 2)      # piece_rows in csrc/cudasp_capi.cu: the call streams in pieces of 2 K1 waves,
-    pieces, cur, b = [], min(piece, max(piece // 8, 8192)), 0     # the first ones ramping up from 1/8 (scan_batch_impl)
-    while b < rows:
-        pieces.append(min(cur, rows - b))
-        b += pieces[-1]
-        cur = min(piece, 2 * cur)
-    h2d = rows * 64 + int(T["outputs"].shape[0]) * 8 + (rows + len(pieces)) * 4
-    d2h = sum((1 + min(c, 1024)) * 4 for c in pieces)
+    # e2e: public host API, host buffers, copies inside the timed region (bytes counted by the library where it issues the copies)
+    ht = args.host_threads if args.host_threads > 0 else None
     for _ in range(2):
-        ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
+        ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"], host_threads=ht)
     assert np.array_equal(ids, T["expected"]), "e2e match set differs from the planted matches"
+    h2d0, d2h0 = q.transfer_bytes()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"])
+        ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"], host_threads=ht)
     torch.cuda.synchronize()
     e2e_ms = 1e3 * (time.perf_counter() - t0) / args.steps
     barrier()
+    h2d1, d2h1 = q.transfer_bytes()
+    h2d, d2h = (h2d1 - h2d0) // args.steps, (d2h1 - d2h0) // args.steps
+    assert np.array_equal(ids, T["expected"]), "e2e match set differs from the planted matches"
     clocks = sampler.finish()
 
     # per-kernel times of one full batch (CUDA events on the launching stream, warm)
@@ -344,21 +466,47 @@ def main():
     for _ in range(3):
         st = M.profile_stages(q, dev, b0["tw"].data_ptr(), b0["out"].data_ptr(), b0["off"].data_ptr(), b0["cnt"], b0["ids"].data_ptr(),
                               b0["n"].data_ptr())
+    q_info = q.info()
+    dev_ms, e2e_ms = S.max_over_ranks(dev_ms / 1e3, dist) * 1e3, S.max_over_ranks(e2e_ms / 1e3, dist) * 1e3
+    # The ranks' part ends here.  Everything below is rank 0 alone: the other ranks leave (their GPUs must be idle for the
+    # one-handle and DuckDB legs, which use every device of the box from ONE process).
+    q.close()
+    del batches, d_tw, d_out, flush
+    torch.cuda.empty_cache()
     if dist:
-        t = torch.tensor([dev_ms, e2e_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, e2e_ms = float(t[0]), float(t[1])
+        dist.barrier()
+        dist.destroy_process_group()
     if rank == 0:
-        peak, peak_src = measured_imad_peak()
+        peak, peak_src, wide_peak = measured_imad_peak()
+        # frac_wide: the ladder's EXECUTED 64-bit multiply-adds (profiles/traffic.json, ncu instruction counts) against the
+        # measured issue rate of IMAD.WIDE itself -- the pipe the kernel is bound by
         value = world * rows / (dev_ms / 1e3)
         e2e = world * rows / (e2e_ms / 1e3)
         ladder_rate = b0["cnt"] * W32_LADDER / (st["ladder"] / 1e3)
-        traffic = None
+        wide_per_row = ladder_wide_per_row(q_info)
+        frac_wide = b0["cnt"] * wide_per_row / (st["ladder"] / 1e3) / wide_peak
+        traffic = fmaheavy = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get("k_ladder_dram_bytes_per_launch")
+            tj = json.load(open(tp))
+            traffic, fmaheavy = tj.get("k_ladder_dram_bytes_per_launch"), tj.get("k_ladder_fmaheavy_pipe_busy")
         cores = os.cpu_count() or 1
         cpu_rate, cpu_n, cpu_dt, _ = cpu_sample(T, min(rows, cores * 6000), cores)
+        cpu_ossl = cpu_openssl_sample(T, min(rows, cores * 1500), cores)
+        one_handle = duck = None
+        if not args.no_legs:
+            try:
+                if world > 1:
+                    one_handle = one_handle_leg(M, T, rows, world, args.batch, min(args.steps, 3))
+            except Exception as ex:      # noqa: BLE001  (a leg must not take the contract line down with it)
+                one_handle = {"unavailable": repr(ex)[:300]}
+            try:
+                if world > 1:      # config C5's shape: 12.5 M rows per GPU (100 M at N = 8), 16 labels, multi-output rows
+                    duck = duckdb_leg(synth, args.duckdb_rows or 12500000, world, 16, 0.25, args.batch, world)
+                else:
+                    duck = duckdb_leg(synth, args.duckdb_rows or 10000000, 1, L, 0.5, args.batch, 1)
+            except Exception as ex:      # noqa: BLE001
+                duck = {"unavailable": repr(ex)[:300]}
         py_base = None
         if world == 1:
             # the reference's only CPU code for this path is its Python verifier (scripts/verify_bip352_test_vector.py);
@@ -394,22 +542,21 @@ def main():
         line = {"metric": metric_name(L), "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u32", "data": "synthetic", "config": config, "clocks": clocks,
-                "e2e": {"value": e2e, "unit": "rows/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "api": "cudasp_scan_batch (C ABI, host buffers -> pinned staging -> async H2D -> kernels -> D2H ids)"},
+                "e2e": {"value": e2e, "unit": "rows/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                        "api": "cudasp_scan_batch (C ABI, host buffers -> pinned staging by the call's host threads -> async H2D -> kernels -> D2H ids)"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "int-mul", "kernel": "k_ladder", "achieved": ladder_rate / 1e12, "peak": peak / 1e12,
-                             "unit": "T IMAD32 lane-ops/s", "frac": ladder_rate / peak, "traffic": traffic,
+                             "unit": "T IMAD32 lane-ops/s", "frac": ladder_rate / peak, "frac_wide": frac_wide, "wide_products_per_row": wide_per_row,
+                             "wide_peak_products_per_s": wide_peak, "fmaheavy_pipe_busy_ncu": fmaheavy, "traffic": traffic,
                              "peak_source": peak_src, "algorithmic_ops_per_row": W32_LADDER, "rows_per_launch": b0["cnt"],
                              "kernel_ms": st["ladder"], "stage_ms": st,
                              "pipeline_frac_per_gpu": (value / world) * w32 / peak, "pipeline_ops_per_row": w32,
                              "hbm_gbs_per_gpu": (value / world) * (64 + 8 * float(T["outputs"].shape[0]) / rows + 4) / 1e9},
                 "cpu_baseline": {"value": cpu_rate, "unit": "rows/s", "cores": cores, "kind": "port",
                                  "sample": "%d rows of the same table, oracle/cudasp_oracle.c, %d pthreads, %.1f s" % (cpu_n, cores, cpu_dt)},
-                "python_baseline": py_base, "gecc_baseline": gecc}
+                "cpu_openssl": cpu_ossl, "python_baseline": py_base, "gecc_baseline": gecc,
+                "one_handle": one_handle, "duckdb": duck}
         emit(line)
-    q.close()
-    if dist:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

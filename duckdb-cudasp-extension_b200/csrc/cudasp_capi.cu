@@ -19,10 +19,12 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/cudasp.h"
 #include "launch.hpp"
+#include "piece_plan.hpp"
 #include "query_plan.hpp"
 #include "staging_internal.hpp"
 
@@ -120,6 +122,7 @@ struct cudasp_query {
   uint32_t rr = 0;               // round-robin cursor for slot acquisition
   std::string err;
   std::atomic<uint64_t> launches{0};
+  std::atomic<uint64_t> h2d_bytes{0}, d2h_bytes{0};   // bytes handed to cudaMemcpyAsync by submit() / finish()
 };
 
 namespace {
@@ -585,6 +588,10 @@ void cudasp_release_cached_memory(void) {
 }
 
 uint64_t cudasp_launch_count(const cudasp_query *q) { return q ? q->launches.load() : 0; }
+void cudasp_transfer_bytes(const cudasp_query *q, uint64_t *h2d, uint64_t *d2h) {
+  if (h2d) *h2d = q ? q->h2d_bytes.load() : 0;
+  if (d2h) *d2h = q ? q->d2h_bytes.load() : 0;
+}
 
 int cudasp_query_info(const cudasp_query *q, int *n_devices, int *ladder_dbl, int *ladder_add, int *fixed_window_bits,
                       int *n_labels) {
@@ -698,6 +705,7 @@ int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t
     CU(q, cudaMemcpyAsync(s->d_tweaks, s->h_tweaks, (size_t)rows * key_bytes(keyfmt), cudaMemcpyHostToDevice, st));
     CU(q, cudaMemcpyAsync(s->d_off, s->h_off, ((size_t)rows + 1) * 4, cudaMemcpyHostToDevice, st));
     if (n_outputs) CU(q, cudaMemcpyAsync(s->d_outputs, s->h_outputs, n_outputs * 8, cudaMemcpyHostToDevice, st));
+    q->h2d_bytes += (uint64_t)rows * key_bytes(keyfmt) + ((uint64_t)rows + 1) * 4 + n_outputs * 8;
   }
   if (trace) cudaEventRecord(s->tr[1], st);
   std::lock_guard<std::mutex> launch_lk(*dc.launch_mu);     // wait -> launches -> record is atomic per device (see DevCtx)
@@ -721,6 +729,7 @@ int submit(cudasp_query *q, Slot *s, uint32_t rows, uint64_t n_outputs, uint64_t
   CU(q, cudaEventRecord(s->ws.free_evt, st));
   const uint32_t eager = std::min<uint32_t>(rows, EAGER_IDS);
   CU(q, cudaMemcpyAsync(s->h_result, s->d_result, ((size_t)eager + 1) * 4, cudaMemcpyDeviceToHost, st));
+  q->d2h_bytes += ((uint64_t)eager + 1) * 4 + (details ? ((uint64_t)std::min(q->details_cap, EAGER_DETAILS) + 1) * sizeof(MatchDetail) : 0);
   CU(q, cudaEventRecord(s->done, st));
   return 0;
 }
@@ -743,6 +752,7 @@ int finish(cudasp_query *q, Slot *s, uint32_t *n_matches) {
     CU(q, cudaMemcpyAsync(s->h_result + 1 + EAGER_IDS, s->d_result + 1 + EAGER_IDS, ((size_t)n - EAGER_IDS) * 4,
                           cudaMemcpyDeviceToHost, s->stream));
     CU(q, cudaStreamSynchronize(s->stream));
+    q->d2h_bytes += ((uint64_t)n - EAGER_IDS) * 4;
   }
   std::sort(s->h_result + 1, s->h_result + 1 + n);
   *n_matches = n;
@@ -933,11 +943,11 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys, const int64_t 
 
 static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
                            const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches,
-                           cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details);
+                           cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details, int host_threads);
 
 int cudasp_scan_batch_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
                           const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches) {
-  return scan_batch_impl(q, tweak_keys, key_format, outputs, out_offsets, rows, match_ids, n_matches, nullptr, 0, nullptr);
+  return scan_batch_impl(q, tweak_keys, key_format, outputs, out_offsets, rows, match_ids, n_matches, nullptr, 0, nullptr, 0);
 }
 
 int cudasp_scan_batch_details(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
@@ -946,7 +956,7 @@ int cudasp_scan_batch_details(cudasp_query *q, const uint8_t *tweak_keys, int ke
   if (!q || !n_details || (details_capacity && !details)) return fail(q, CUDASP_ERR_ARG, "NULL argument");
   if (!q->details_cap) return fail(q, CUDASP_ERR_STATE, "match details are not enabled: call cudasp_query_enable_details first");
   return scan_batch_impl(q, tweak_keys, key_format, outputs, out_offsets, rows, match_ids, n_matches, details, details_capacity,
-                         n_details);
+                         n_details, 0);
 }
 
 int cudasp_query_enable_details(cudasp_query *q, uint32_t max_details_per_batch) {
@@ -968,11 +978,17 @@ int cudasp_result_details(cudasp_query *q, const cudasp_result *r, const cudasp_
   return CUDASP_OK;
 }
 
+// The synchronous call: a host table in, matching row ids out.  The table is cut into pieces -- at most `piece_rows` rows
+// (whole K1 waves), ramping up over the first pieces (1/8, 1/4, 1/2: the GPUs start after a short first copy) and down over
+// the last ones (the tail the GPUs finish alone after the last copy is short) -- and `host_threads` staging threads take
+// pieces in order: acquire a slot (devices in turn), memcpy into its pinned buffers, submit, and collect their own oldest
+// piece whenever no slot is free.  One thread cannot keep one B200 busy from pageable memory (a 64 B/row memcpy at ~5 GB/s is
+// as slow as the scan itself); several threads over one handle that owns several devices are the in-process form of the
+// reference's "DuckDB workers round-robin onto GPUs" (src/cudasp_extension.cu:516-532).
 static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
                            const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches,
-                           cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details) {
+                           cudasp_match_detail *details, uint32_t details_capacity, uint32_t *n_details, int host_threads) {
   if (n_details) *n_details = 0;
-  uint32_t total_det = 0;
   if (key_format != CUDASP_KEYS_XY64 && key_format != CUDASP_KEYS_SEC1_33) return fail(q, CUDASP_ERR_ARG, "unknown key format");
   const size_t kb = key_bytes(key_format);
   if (!q || !n_matches) return fail(q, CUDASP_ERR_ARG, "NULL argument");
@@ -980,107 +996,164 @@ static int scan_batch_impl(cudasp_query *q, const uint8_t *tweak_keys, int key_f
   if (rows == 0) return CUDASP_OK;
   if (!tweak_keys || !match_ids) return fail(q, CUDASP_ERR_ARG, "NULL argument");
   if (out_offsets && !outputs && out_offsets[rows] != out_offsets[0]) return fail(q, CUDASP_ERR_ARG, "outputs is NULL");
-  struct Pending { Slot *s; uint32_t base; };
-  std::deque<Pending> pending;
-  uint32_t total = 0;
-  int rc = 0;
   static const bool trace = getenv("CUDASP_TRACE") != nullptr;     // coarse host-side timings to stderr
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   const double t_begin = trace ? now() : 0;
-  double t_copy = 0, t_submit = 0, t_wait = 0;
-  auto collect = [&](Pending p) -> int {
+
+  // ---- the piece list
+  const uint32_t piece = std::min<uint32_t>(q->batch_rows, q->piece_rows);
+  const uint32_t nd = (uint32_t)q->devs.size();
+  const std::vector<uint32_t> starts = piece_plan(rows, piece, nd, RAMP_DIV);      // piece i = rows [starts[i], starts[i + 1])
+  const uint32_t n_pieces = (uint32_t)starts.size() - 1;
+  if (host_threads <= 0) {      // auto: enough copy threads to feed the devices, not more than there are pieces or cores
+    const char *e = getenv("CUDASP_HOST_THREADS");
+    host_threads = e && atoi(e) > 0 ? atoi(e) : (int)std::min<uint32_t>(4u * nd, std::max(1u, std::thread::hardware_concurrency() / 2));
+  }
+  host_threads = (int)std::max<uint32_t>(1u, std::min<uint32_t>((uint32_t)host_threads, std::min<uint32_t>(n_pieces / 2, 64u)));
+
+  struct Pending { Slot *s; uint32_t base; };
+  struct Worker {
+    std::deque<Pending> pending;
+    std::vector<uint32_t> ids;
+    std::vector<cudasp_match_detail> det;
+    uint64_t n_det = 0;          // found (may exceed what is kept when the caller's capacity is smaller)
+    int rc = 0;
+    double t_copy = 0, t_submit = 0, t_wait = 0;
+  };
+  std::vector<Worker> workers((size_t)host_threads);
+  std::atomic<uint32_t> next_piece{0};
+  std::atomic<bool> failed{false};
+
+  auto collect = [&](Worker &w, Pending p) -> int {
     uint32_t n = 0;
     const double tw = trace ? now() : 0;
     int r = finish(q, p.s, &n);
-    if (trace) t_wait += now() - tw;
+    if (trace) w.t_wait += now() - tw;
     if (!r && p.s->det_truncated) r = fail(q, CUDASP_ERR_STATE, "more match details than max_details_per_batch: raise it");
     if (!r) {
-      for (uint32_t i = 0; i < n; i++) match_ids[total + i] = p.base + p.s->h_result[1 + i];
-      total += n;
+      for (uint32_t i = 0; i < n; i++) w.ids.push_back(p.base + p.s->h_result[1 + i]);
       if (n_details) {
-        for (uint32_t i = 0; i < p.s->n_det; i++, total_det++) {
-          if (total_det >= details_capacity) continue;       // counted, not stored
-          memcpy(&details[total_det], &p.s->h_det[1 + i], sizeof(cudasp_match_detail));
-          details[total_det].row += p.base;
+        for (uint32_t i = 0; i < p.s->n_det; i++, w.n_det++) {
+          if (w.det.size() >= details_capacity) continue;       // counted, not stored
+          cudasp_match_detail d;
+          memcpy(&d, &p.s->h_det[1 + i], sizeof d);
+          d.row += p.base;
+          w.det.push_back(d);
         }
       }
     }
     release_slot(q, p.s);
     return r;
   };
-  // Pieces smaller than batch_rows: the first H2D copy is short, so the GPU starts early, and the memcpy of
-  // piece k+1 into pinned memory overlaps the kernels of piece k (separate slots, separate streams).
-  // The first pieces ramp up (1/8, 1/4, 1/2 of a full piece): the host copy of a full first piece would leave the GPU
-  // idle for ~1.5 ms at the start of every call.
-  const uint32_t piece = std::min<uint32_t>(q->batch_rows, q->piece_rows);
-  uint32_t cur = std::min(piece, std::max<uint32_t>(piece / RAMP_DIV, 8192u));
-  for (uint32_t base = 0, cnt = 0; base < rows && !rc; base += cnt, cur = std::min<uint64_t>(piece, 2ull * cur)) {
-    cnt = std::min<uint32_t>(cur, rows - base);
-    Slot *s = nullptr;
-    while (!s) {
-      s = try_acquire(q, &rc);
-      if (s || rc) break;
-      if (!pending.empty()) {          // recycle our own oldest batch (results stay in row order)
-        Pending p = pending.front();
-        pending.pop_front();
-        rc = collect(p);
-        if (rc) break;
+  auto run = [&](Worker &w) {
+    int rc = 0;
+    while (!rc && !failed.load(std::memory_order_relaxed)) {
+      const uint32_t pi = next_piece.fetch_add(1);
+      if (pi >= n_pieces) break;
+      const uint32_t base = starts[pi], cnt = starts[pi + 1] - base;
+      Slot *s = nullptr;
+      while (!s) {
+        s = try_acquire(q, &rc);
+        if (s || rc) break;
+        if (!w.pending.empty()) {          // recycle our own oldest piece
+          Pending p = w.pending.front();
+          w.pending.pop_front();
+          rc = collect(w, p);
+          if (rc) break;
+        } else {
+          s = acquire_blocking(q, &rc);
+          if (!s) break;
+        }
+      }
+      if (rc || !s) break;
+      s->internal = true;
+      const uint32_t o0 = out_offsets ? out_offsets[base] : 0;
+      if (out_offsets && out_offsets[base + cnt] < o0) {
+        release_slot(q, s);
+        rc = fail(q, CUDASP_ERR_ARG, "out_offsets is not monotonically non-decreasing");
+        break;
+      }
+      const uint64_t no = out_offsets ? (uint64_t)(out_offsets[base + cnt] - o0) : 0;
+      if (no > s->cap_outputs) {
+        cudaSetDevice(q->devs[s->dev_index].device);
+        cudaStreamSynchronize(s->stream);
+        rc = alloc_slot_outputs(q, *s, no + no / 4);
+        if (rc) { release_slot(q, s); break; }
+      }
+      const double tc = trace ? now() : 0;
+      memcpy(s->h_tweaks, tweak_keys + (size_t)base * kb, (size_t)cnt * kb);
+      if (out_offsets) {
+        // rebase, and refuse a non-monotonic offset array: K5/K7/K8 index the outputs with these, unchecked
+        uint32_t prev = 0, bad = 0;
+        for (uint32_t i = 0; i <= cnt; i++) {
+          const uint32_t v = out_offsets[base + i] - o0;
+          bad |= (uint32_t)(v < prev);
+          s->h_off[i] = prev = v;
+        }
+        if (bad) { release_slot(q, s); rc = fail(q, CUDASP_ERR_ARG, "out_offsets is not monotonically non-decreasing"); break; }
+        if (no) memcpy(s->h_outputs, outputs + o0, no * 8);
       } else {
-        s = acquire_blocking(q, &rc);
-        if (!s) break;
+        memset(s->h_off, 0, ((size_t)cnt + 1) * 4);
       }
-    }
-    if (rc) break;
-    s->internal = true;
-    const uint32_t o0 = out_offsets ? out_offsets[base] : 0;
-    if (out_offsets && out_offsets[base + cnt] < o0) {
-      release_slot(q, s);
-      rc = fail(q, CUDASP_ERR_ARG, "out_offsets is not monotonically non-decreasing");
-      break;
-    }
-    const uint64_t no = out_offsets ? (uint64_t)(out_offsets[base + cnt] - o0) : 0;
-    if (no > s->cap_outputs) {
-      cudaSetDevice(q->devs[s->dev_index].device);
-      cudaStreamSynchronize(s->stream);
-      rc = alloc_slot_outputs(q, *s, no + no / 4);
+      const double ts = trace ? now() : 0;
+      rc = submit(q, s, cnt, no, 0, key_format);
+      if (trace) { w.t_copy += ts - tc; w.t_submit += now() - ts; }
       if (rc) { release_slot(q, s); break; }
+      w.pending.push_back({s, base});
     }
-    const double tc = trace ? now() : 0;
-    memcpy(s->h_tweaks, tweak_keys + (size_t)base * kb, (size_t)cnt * kb);
-    if (out_offsets) {
-      // rebase, and refuse a non-monotonic offset array: K5/K7/K8 index the outputs with these, unchecked
-      uint32_t prev = 0, bad = 0;
-      for (uint32_t i = 0; i <= cnt; i++) {
-        const uint32_t v = out_offsets[base + i] - o0;
-        bad |= (uint32_t)(v < prev);
-        s->h_off[i] = prev = v;
-      }
-      if (bad) { release_slot(q, s); rc = fail(q, CUDASP_ERR_ARG, "out_offsets is not monotonically non-decreasing"); break; }
-      if (no) memcpy(s->h_outputs, outputs + o0, no * 8);
-    } else {
-      memset(s->h_off, 0, ((size_t)cnt + 1) * 4);
+    if (rc) failed.store(true);
+    while (!w.pending.empty()) {
+      Pending p = w.pending.front();
+      w.pending.pop_front();
+      int r = collect(w, p);
+      if (!rc) rc = r;
     }
-    const double ts = trace ? now() : 0;
-    rc = submit(q, s, cnt, no, 0, key_format);
-    if (trace) { t_copy += ts - tc; t_submit += now() - ts; }
-    if (rc) { release_slot(q, s); break; }
-    pending.push_back({s, base});
+    w.rc = rc;
+  };
+  if (host_threads == 1) {
+    run(workers[0]);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 1; t < host_threads; t++) th.emplace_back([&, t] { run(workers[(size_t)t]); });
+    run(workers[0]);
+    for (auto &t : th) t.join();
   }
-  while (!pending.empty()) {
-    Pending p = pending.front();
-    pending.pop_front();
-    int r = collect(p);
-    if (!rc) rc = r;
+  int rc = 0;
+  uint32_t total = 0;
+  uint64_t total_det = 0;
+  for (Worker &w : workers) {
+    if (w.rc && !rc) rc = w.rc;
+    if (total + w.ids.size() <= rows) memcpy(match_ids + total, w.ids.data(), w.ids.size() * 4);
+    total += (uint32_t)w.ids.size();
+    total_det += w.n_det;
   }
-  *n_matches = total;
+  if (!rc && total > rows) rc = fail(q, CUDASP_ERR_STATE, "internal: more matches than rows");
+  if (!rc) std::sort(match_ids, match_ids + total);      // pieces are disjoint row ranges: ascending ids over the whole call
+  *n_matches = rc ? 0 : total;
   if (n_details) {
-    *n_details = total_det;
+    std::vector<cudasp_match_detail> all;
+    for (Worker &w : workers) all.insert(all.end(), w.det.begin(), w.det.end());
+    std::sort(all.begin(), all.end(), [](const cudasp_match_detail &a, const cudasp_match_detail &b) {
+      return a.row != b.row ? a.row < b.row : a.k < b.k;
+    });
+    const size_t keep = std::min<size_t>(all.size(), details_capacity);
+    if (keep) memcpy(details, all.data(), keep * sizeof(cudasp_match_detail));
+    *n_details = (uint32_t)std::min<uint64_t>(total_det, 0xffffffffull);
     if (!rc && total_det > details_capacity) rc = fail(q, CUDASP_ERR_ARG, "details capacity too small (n_details holds the number found)");
   }
-  if (trace)
-    fprintf(stderr, "[cudasp] scan_batch %u rows: total %.3f ms, host copy %.3f, submit calls %.3f, waiting for the GPU %.3f\n", rows,
-            1e3 * (now() - t_begin), 1e3 * t_copy, 1e3 * t_submit, 1e3 * t_wait);
+  if (trace) {
+    double c = 0, sb = 0, wt = 0;
+    for (Worker &w : workers) { c += w.t_copy; sb += w.t_submit; wt += w.t_wait; }
+    fprintf(stderr, "[cudasp] scan_batch %u rows, %u pieces, %d host thread(s): total %.3f ms; summed over threads: host copy %.3f, "
+                    "submit calls %.3f, waiting for the GPU %.3f\n", rows, n_pieces, host_threads, 1e3 * (now() - t_begin), 1e3 * c,
+            1e3 * sb, 1e3 * wt);
+  }
   return rc;
+}
+
+int cudasp_scan_batch_mt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                         const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches, int host_threads) {
+  return scan_batch_impl(q, tweak_keys, key_format, outputs, out_offsets, rows, match_ids, n_matches, nullptr, 0, nullptr, host_threads);
 }
 
 // ---- device-resident entry ------------------------------------------------------------

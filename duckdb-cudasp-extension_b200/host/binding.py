@@ -46,7 +46,7 @@ EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "c
            "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory",
            "cudasp_scan_batch_fmt", "cudasp_submit_slot_fmt", "cudasp_scan_candidates_fmt",
            "cudasp_query_enable_details", "cudasp_result_details", "cudasp_scan_batch_details", "cudasp_debug_gtab",
-           "cudasp_device_sm_count"]
+           "cudasp_device_sm_count", "cudasp_scan_batch_mt", "cudasp_transfer_bytes"]
 
 
 def lib():
@@ -82,6 +82,9 @@ def lib():
         L.cudasp_test_field.argtypes = [C.c_int, C.c_int, vp, vp, vp, C.c_uint32]
         L.cudasp_debug_gtab.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, vp]
         L.cudasp_device_sm_count.argtypes = [C.c_int]
+        L.cudasp_scan_batch_mt.argtypes = [vp, vp, C.c_int, vp, vp, C.c_uint32, vp, u32p, C.c_int]
+        L.cudasp_transfer_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.cudasp_transfer_bytes.restype = None
         L.cudasp_launch_count.argtypes = [vp]
         L.cudasp_launch_count.restype = C.c_uint64
         L.cudasp_query_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 5
@@ -153,8 +156,14 @@ class Query:
     def launch_count(self) -> int:
         return int(lib().cudasp_launch_count(self._h))
 
+    def transfer_bytes(self):
+        """(host->device, device->host) bytes this query has copied so far."""
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        lib().cudasp_transfer_bytes(self._h, C.byref(a), C.byref(b))
+        return int(a.value), int(b.value)
+
     def scan_batch(self, tweaks: np.ndarray, outputs: Optional[np.ndarray], out_offsets: Optional[np.ndarray],
-                   key_format: int = KEYS_XY64) -> np.ndarray:
+                   key_format: int = KEYS_XY64, host_threads: Optional[int] = None) -> np.ndarray:
         """tweaks uint8 [rows,64] (or [rows,33] with key_format=KEYS_SEC1_33); outputs int64 [n]; out_offsets uint32
         [rows+1] -> ascending matching row ids."""
         tweaks = np.ascontiguousarray(tweaks, dtype=np.uint8).reshape(-1, KEY_BYTES[key_format])
@@ -166,7 +175,10 @@ class Query:
         ids = np.zeros(max(rows, 1), np.uint32)
         n = C.c_uint32(0)
         outp = _ptr(outputs) if out_offsets is not None else None
-        if key_format == KEYS_XY64:     # the reference-shaped entry point
+        if host_threads is not None:
+            self._check(lib().cudasp_scan_batch_mt(self._h, _ptr(tweaks), key_format, outp, _ptr(out_offsets), rows, _ptr(ids),
+                                                   C.byref(n), int(host_threads)))
+        elif key_format == KEYS_XY64:     # the reference-shaped entry point
             self._check(lib().cudasp_scan_batch(self._h, _ptr(tweaks), outp, _ptr(out_offsets), rows, _ptr(ids), C.byref(n)))
         else:
             self._check(lib().cudasp_scan_batch_fmt(self._h, _ptr(tweaks), key_format, outp, _ptr(out_offsets), rows, _ptr(ids),

@@ -102,6 +102,13 @@ int cudasp_scan_batch(cudasp_query *q, const uint8_t *tweak_keys /* rows * 64 B 
 int cudasp_scan_batch_fmt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
                           const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches);
 
+/* Same with the number of host staging threads chosen by the caller (0 = automatic: up to 4 per device, as many as there are
+ * pieces and cores; cudasp_scan_batch / _fmt use the automatic choice).  The call cuts the table into pieces of at most two
+ * ladder waves, ramping up at the start and down at the end; each staging thread copies pieces into pinned slots (devices in
+ * turn) and submits them, so one call over a handle that owns N devices feeds all N from one host table. */
+int cudasp_scan_batch_mt(cudasp_query *q, const uint8_t *tweak_keys, int key_format, const int64_t *outputs,
+                         const uint32_t *out_offsets, uint32_t rows, uint32_t *match_ids, uint32_t *n_matches, int host_threads);
+
 /* ---- streaming: pinned double-buffered staging, async H2D on per-device streams -------------
  * The host fills a pinned slot directly from its column vectors (what AccumulateInput does into
  * std::vectors, src/cudasp_extension.cu:154-224), submits it, and collects results later. */
@@ -207,6 +214,8 @@ int cudasp_test_field(int device, int op, const uint8_t *a, const uint8_t *b, ui
 int cudasp_debug_gtab(int device, uint32_t window, uint32_t first_digit, uint32_t n, uint8_t *out);
 /* Counters: number of kernel launches issued by this query so far; ladder schedule shape. */
 uint64_t cudasp_launch_count(const cudasp_query *q);
+/* Bytes this query has handed to host->device and device->host copies so far (bench.py's e2e accounting). */
+void cudasp_transfer_bytes(const cudasp_query *q, uint64_t *h2d, uint64_t *d2h);
 int cudasp_query_info(const cudasp_query *q, int *n_devices, int *ladder_dbl, int *ladder_add, int *fixed_window_bits,
                       int *n_labels);
 const char *cudasp_version(void);

@@ -196,3 +196,13 @@ def gtab_offset(w):
     out = np.zeros(32, np.uint8)
     lib.hc_gtab_offset(w, _p(out))
     return int.from_bytes(out.tobytes(), "little")
+
+
+def piece_plan(rows, piece, n_devices):
+    """starts of the pieces cudasp_scan_batch cuts `rows` rows into (csrc/piece_plan.hpp)."""
+    lib = load()
+    cap = rows // max(min(piece, 8192), 1) + 64 * n_devices + 8
+    out = np.zeros(cap, np.uint32)
+    n = lib.hc_piece_plan(rows, piece, n_devices, out.ctypes.data_as(C.POINTER(C.c_uint32)), cap)
+    assert 0 <= n < cap
+    return out[: n + 1].tolist()

@@ -30,7 +30,15 @@ void batch_inv_all(std::vector<fe> &vals, uint32_t T) {
 }
 }  // namespace
 
+#include "piece_plan.hpp"
 extern "C" {
+// starts of the pieces the synchronous call cuts `rows` into (csrc/piece_plan.hpp); returns the number of pieces
+int hc_piece_plan(uint32_t rows, uint32_t piece, uint32_t n_devices, uint32_t *starts, uint32_t cap) {
+  const std::vector<uint32_t> s = csp::piece_plan(rows, piece, n_devices);
+  for (size_t i = 0; i < s.size() && i < cap; i++) starts[i] = s[i];
+  return (int)s.size() - 1;
+}
+
 
 // op 0 mul, 1 sqr, 2 add, 3 sub, 4 inv, 5 normalize, 6 neg, 7 lin2<1,-8>, 8 lin3<1,-1,-2>(a,b,b), 9 lin2<4,-1>
 int hc_field(int op, const uint8_t *a, const uint8_t *b, uint8_t *out, uint32_t n) {

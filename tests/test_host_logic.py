@@ -320,3 +320,22 @@ def test_details_row_against_reference_generated_chain(golden):
         sk = int(tx["sk"], 16).to_bytes(32, "little")
         got = H.details_row(sk, enc(tx["spend"]), [enc(l) for l in tx["labels"]], enc(tx["S"]), tx["outputs"])
         assert got == [(r["k"], r["output_index"], r["label_index"], int(r["t"], 16)) for r in tx["records"]]
+
+
+def test_piece_plan_covers_the_table_and_ramps_at_both_ends():
+    """cudasp_scan_batch's piece list: every row exactly once, no piece above the limit, short pieces first (and last, when the
+    table has a middle), one round of devices per size."""
+    piece = 151552                       # two ladder waves on a B200
+    for rows in (1, 5, 8192, 8193, 100000, 300000, 1000000, 9400000, 75200000):
+        for nd in (1, 2, 8):
+            s = H.piece_plan(rows, piece, nd)
+            sizes = [b - a for a, b in zip(s, s[1:])]
+            assert s[0] == 0 and s[-1] == rows and all(0 < x <= piece for x in sizes)
+            if rows >= 9400000:
+                assert sizes[:nd] == [piece // 8] * nd and sizes[nd:2 * nd] == [piece // 4] * nd      # ramp up ...
+                assert sizes[-nd:] == [piece // 8] * nd and sizes[-2 * nd:-nd] == [piece // 4] * nd   # ... and down
+                mid = sizes[3 * nd:-3 * nd]
+                assert all(x == piece for x in mid[:-1])
+    assert H.piece_plan(0, piece, 1) == [0]
+    s = H.piece_plan(20000, 1000, 1)          # pieces smaller than the ramp's floor: no ramp
+    assert set(b - a for a, b in zip(s, s[1:])) == {1000}
