@@ -17,6 +17,8 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 DUCKDB = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "duckdb_ext", "bin", "duckdb")
+# --impl reference: the REFERENCE's own extension in the same DuckDB (oracle/_ref/duckdb_ref, `make -C oracle ref_ext`)
+DUCKDB_REF = os.path.join(ROOT, "oracle", "_ref", "duckdb_ref")
 
 
 def blob(b: bytes) -> str:
@@ -34,6 +36,7 @@ def main():
     ap.add_argument("--compressed", action="store_true", help="store tweak_key as 33-byte SEC1 (decompressed on the GPU)")
     ap.add_argument("--details", action="store_true", help="details := true (one result row per found output)")
     ap.add_argument("--in-memory", action="store_true", help="load the table into a DuckDB table first (no Parquet decode in the timed query)")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "both"], help="which extension runs the SQL (same file, same query)")
     a = ap.parse_args()
     import numpy as np
     import pyarrow as pa
@@ -60,7 +63,11 @@ def main():
     gen_s = time.perf_counter() - t0
     labels = "[" + ", ".join(blob(l) for l in T["labels"]) + "]" + ("" if T["labels"] else "::BLOB[]")
     src = "read_parquet('%s')" % path if a.replicate == 1 else "read_parquet([%s])" % ", ".join(["'%s'" % path] * a.replicate)
-    for threads in [int(x) for x in a.threads.split(',')]:
+    impls = ["ours", "reference"] if a.impl == "both" else [a.impl]
+    for threads, impl in [(int(x), i) for x in a.threads.split(',') for i in impls]:
+        exe = DUCKDB if impl == "ours" else DUCKDB_REF
+        if impl == "reference" and (a.compressed or a.details):
+            continue                      # the reference has neither
         pre = "PRAGMA threads=%d;\n" % threads if threads else ""
         cur = src
         if a.in_memory:
@@ -70,7 +77,7 @@ def main():
             cur, blob(T["sk"]), blob(T["spend"]), labels, a.batch, ", details := true" if a.details else "")
         plain = "SELECT count(*), sum(height), sum(octet_length(tweak_key)), sum(len(outputs)) FROM %s;" % cur
         sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + "SELECT current_setting('threads');\n"
-        p = subprocess.run([DUCKDB, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
+        p = subprocess.run([exe, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
         if os.environ.get("CUDASP_TRACE"):
             sys.stderr.write(p.stderr)
         lines = [l for l in p.stdout.strip().splitlines() if l]
@@ -79,7 +86,7 @@ def main():
         want = len(T["expected"]) * a.replicate
         rows = a.rows * a.replicate
         ok = p.returncode == 0 and len(vals) >= 2 and int(vals[0]) == want and int(vals[1]) == want
-        res = {"rows": rows, "replicate": a.replicate, "geom_p": a.geom_p, "mean_outputs": float(len(T["outputs"])) / a.rows, "labels": a.labels, "compressed": a.compressed, "details": a.details, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
+        res = {"impl": impl, "rows": rows, "replicate": a.replicate, "geom_p": a.geom_p, "mean_outputs": float(len(T["outputs"])) / a.rows, "labels": a.labels, "compressed": a.compressed, "details": a.details, "threads": vals[-1] if vals else None, "in_memory": a.in_memory, "matches_expected": want,
                "matches_ok": ok, "scan_s_cold": times[0] if times else None, "scan_s_warm": times[1] if len(times) > 1 else None,
                "plain_read_s": times[2] if len(times) > 2 else None, "gen_s": round(gen_s, 1),
                "rows_per_s_warm": rows / times[1] if len(times) > 1 else None, "stderr": p.stderr[-300:]}
