@@ -46,7 +46,7 @@ EXPORTS = ["cudasp_device_count", "cudasp_last_error", "cudasp_query_create", "c
            "cudasp_launch_count", "cudasp_query_info", "cudasp_version", "cudasp_query_create_ex", "cudasp_try_acquire_slot", "cudasp_release_cached_memory",
            "cudasp_scan_batch_fmt", "cudasp_submit_slot_fmt", "cudasp_scan_candidates_fmt",
            "cudasp_query_enable_details", "cudasp_result_details", "cudasp_scan_batch_details", "cudasp_debug_gtab",
-           "cudasp_device_sm_count", "cudasp_scan_batch_mt", "cudasp_transfer_bytes"]
+           "cudasp_device_sm_count", "cudasp_scan_batch_mt", "cudasp_transfer_bytes", "cudasp_batch_inverse_static"]
 
 
 def lib():
@@ -85,6 +85,7 @@ def lib():
         L.cudasp_scan_batch_mt.argtypes = [vp, vp, C.c_int, vp, vp, C.c_uint32, vp, u32p, C.c_int]
         L.cudasp_transfer_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.cudasp_transfer_bytes.restype = None
+        L.cudasp_batch_inverse_static.argtypes = [C.c_int, vp, vp, C.c_uint32, vp]
         L.cudasp_launch_count.argtypes = [vp]
         L.cudasp_launch_count.restype = C.c_uint64
         L.cudasp_query_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 5

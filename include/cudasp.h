@@ -207,6 +207,19 @@ int cudasp_scan_intermediates(cudasp_query *q, const uint8_t *tweak_keys, uint32
                               uint8_t *S_le, uint8_t *t_be, uint8_t *P0_le);
 /* Field KATs on the device: op 0 mul, 1 sqr(a), 2 add, 3 sub, 4 inv(a), 5 normalize(a); n elements of 32 B LE. */
 int cudasp_test_field(int device, int op, const uint8_t *a, const uint8_t *b, uint8_t *out, uint32_t n);
+/* ---- allocation-free entry (no counterpart in the reference) ----------
+ * For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): a variant
+ * of the pipeline's batch-inversion kernel (Montgomery's trick, one Fermat inversion per 16 elements) whose scratch is a
+ * static __device__ array inside the library -- CUDASP_STATIC_INV_MAX elements = 2 MB per GPU that loads the library, held
+ * until the process exits -- instead of a cudaMalloc'ed workspace.  d_out[i] = d_in[i]^-1 mod p (p = 2^256 - 2^32 - 977),
+ * canonical, 0 -> 0; elements are 32 B little-endian, both pointers are DEVICE pointers on `device`, 16-byte aligned, and
+ * may be equal (in place).  Asynchronous on `stream` (a cudaStream_t; 0 = the default stream).  n > CUDASP_STATIC_INV_MAX
+ * is refused with CUDASP_ERR_ARG.  The call itself allocates nothing (no cudaMalloc / cudaFree, no allocating library
+ * routine).  All calls on one device share the one scratch array: calls that overlap on the GPU (different streams, no
+ * dependency between them) race -- serialise them.  Nothing in the scratch has to start at zero and nothing is cleared. */
+#define CUDASP_STATIC_INV_MAX 65536u
+int cudasp_batch_inverse_static(int device, const uint8_t *d_in, uint8_t *d_out, uint32_t n, void *stream);
+
 /* n entries of the device's fixed-base table, window `window`, digits first_digit .. first_digit+n-1, 64 B LE x||y each:
  * entry (w, d) must be (d * 2^(bits*w) + r_w) * G (bits = cudasp_query_info's fixed_window_bits).  The table is built
  * on the device once per process (it replaces the reference's host-uploaded 2^i*G table, gECC gsv.h:1094-1122); the
