@@ -113,6 +113,7 @@ struct cudasp_query {
   uint32_t batch_rows = 0;
   uint64_t max_outputs = 0;
   uint32_t details_cap = 0;      // > 0: match details enabled, records per batch
+  uint32_t wave_threads = 0;     // threads of one full wave of the 128-register kernels: SMs x 4 blocks x 128
   uint32_t piece_rows = 0;       // rows per piece of the synchronous call: whole K1 waves (SMs x 4 blocks x 128 rows)
   std::vector<DevCtx> devs;
   std::vector<Slot *> all_slots;
@@ -451,7 +452,12 @@ int launch_pipeline(cudasp_query *q, DevCtx &dc, Workspace &w, const uint8_t *d_
   if (L) {
     const uint64_t n64 = (uint64_t)rows * L;
     if (n64 > 0xffffffffull) return fail(q, CUDASP_ERR_ARG, "rows * labels exceeds 2^32");
-    CU(q, launch::batch_inv(w.D, w.DS, (uint32_t)n64, per, st));
+    // The label denominators are rows * L elements: with many labels there are threads to spare, so more elements share one
+    // Fermat inversion (255 S + 15 M per thread whatever it inverts): 16 per thread costs (48 + 270) / 16 = 20 field operations
+    // per element, 64 per thread 7.  Keep about four warps per scheduler (q->wave_threads) in flight, never fewer than `per`.
+    static const bool fixed_per = getenv("CUDASP_INV_PER_THREAD") != nullptr;
+    const uint32_t per_labels = fixed_per ? per : (uint32_t)std::min<uint64_t>(128, std::max<uint64_t>(per, n64 / std::max(q->wave_threads, 1u)));
+    CU(q, launch::batch_inv(w.D, w.DS, (uint32_t)n64, per_labels, st));
     mark();
     CU(q, launch::final_labels(w.X, w.Y, w.D, rows, d_outputs, d_off, dc.d_labels, L, w.flags, d_ids, d_count, d_cands, inv_flags, st));
     nl += 2;
@@ -549,7 +555,8 @@ int cudasp_query_create_ex(const uint8_t scan_private_key[32], const uint8_t spe
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, devs[0]);
     const char *pw = getenv("CUDASP_PIECE_WAVES");            // tuning aid
     const uint32_t waves = pw && atoi(pw) > 0 ? (uint32_t)atoi(pw) : SYNC_PIECE_WAVES;
-    q->piece_rows = (uint32_t)sms * 4u * 128u * waves;
+    q->wave_threads = (uint32_t)sms * 4u * 128u;
+    q->piece_rows = q->wave_threads * waves;
   }
   q->all_slots.reserve(devs.size() * slots_per_device);   // never reallocates: ids stay valid without the lock
   // Only the FIRST device is brought up here (context, fixed-base table, one slot), so that key and device errors surface
