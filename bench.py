@@ -193,7 +193,30 @@ def reference_arm(args, config, cores, synth):
     assert np.array_equal(np.nonzero(flags)[0], Tc["expected"][Tc["expected"] < n]), "oracle disagrees with planted matches"
     cpu_port = {"value": cpu_rate, "unit": "rows/s", "cores": cores, "kind": "port",
                 "sample": "%d rows, oracle/cudasp_oracle.c, %d pthreads, %.1f s" % (n, cores, dt)}
-    if use_gecc:
+    ref_exe = os.path.join(ROOT, "oracle", "_ref", "duckdb_ref")
+    gpu_ok = False
+    try:
+        import torch
+        gpu_ok = torch.cuda.is_available() and torch.cuda.device_count() >= args.gpus
+    except Exception:
+        pass
+    if gpu_ok and os.path.exists(ref_exe) and not os.environ.get("CUDASP_REFERENCE_ARM_FFI"):
+        # First choice: the reference's own DuckDB extension through its own SQL surface, all N GPUs from ONE DuckDB process (its
+        # own multi-GPU mode).  One table of rows_per_gpu rows (the full C3 table at N = 1; a bounded sample of the N x larger
+        # weak-scaling workload at N > 1 -- the reference needs ~4.5 s for it on one B200).
+        rows = args.rows
+        T = synth.make_table(rows, seed, n_labels=L, n_base=n_base, n_per_label=per_label, batch_rows=args.batch)
+        os.environ["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(args.gpus))
+        value, ms, ts = reference_sql_run(ref_exe, synth, T, rows, L, args.batch, args.steps, max(args.warmup, 1))
+        base.update({"value": value, "ms_per_step": ms, "dtype": "u32",
+                     "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "reference",
+                                      "sample": "the UNMODIFIED reference DuckDB extension (src/cudasp_extension.cu + src/cudasp_gpu.cu + gECC, compiled for "
+                                                "sm_100 into oracle/_ref/duckdb_ref by `make -C oracle ref_ext`) running its README's SQL on a %d-row Parquet "
+                                                "table (%d labels, batch_size %d) with %d DuckDB threads on %d B200; match count equal to the planted matches; "
+                                                "the reference has no CPU implementation of this path" % (rows, L, args.batch, cores, args.gpus)},
+                     "cpu_port": cpu_port, "step_seconds": ts,
+                     "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    elif use_gecc:
         per_gpu = min(args.rows, REF_SAMPLE_ROWS)   # bounded sample: the reference needs ~1.3 s per million rows
         rows = per_gpu * args.gpus                  # weak scaling: the same sample on each of N GPUs
         T = synth.make_table(rows, seed, n_labels=L, n_base=n_base, n_per_label=per_label, batch_rows=args.batch)
@@ -229,6 +252,62 @@ def cpu_openssl_sample(T, rows_sample, threads):
                 "sample": "%d rows of the same table, %d threads, %.1f s" % (n, threads, dt)}
     except Exception as ex:      # noqa: BLE001  (the baseline is optional; the product line must still print)
         return {"unavailable": repr(ex)[:200]}
+
+
+def sql_blob(b):
+    return "'" + "".join("\\x%02x" % c for c in b) + "'::BLOB"
+
+
+def write_parquet_table(synth, rows_file, labels, geom_p, batch, table=None):
+    """A synthetic table (tests/synth.py: valid curve points, planted matches) as an uncompressed Parquet file with the reference's
+    four columns.  -> (table dict, path, directory, seconds spent)"""
+    import tempfile
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    t0 = time.perf_counter()
+    T = table
+    if T is None:
+        seed = 352005 if labels == 16 else 352003
+        T = synth.make_table(rows_file, seed, n_labels=labels, n_base=1000 if labels == 16 else 100, n_per_label=100 if labels else 0,
+                             batch_rows=batch, geom_p=geom_p, max_extra=63 if geom_p < 0.5 else 15)
+    off = T["offsets"].astype(np.int64)
+    tw = pa.FixedSizeBinaryArray.from_buffers(pa.binary(64), rows_file, [None, pa.py_buffer(T["tweaks"].tobytes())]).cast(pa.binary())
+    txid = np.zeros((rows_file, 32), np.uint8)
+    txid[:, :8] = np.arange(rows_file, dtype=np.uint64).view(np.uint8).reshape(rows_file, 8)
+    tx = pa.FixedSizeBinaryArray.from_buffers(pa.binary(32), rows_file, [None, pa.py_buffer(txid.tobytes())]).cast(pa.binary())
+    outs = pa.ListArray.from_arrays(pa.array(off.astype(np.int32), pa.int32()), pa.array(T["outputs"], pa.int64()))
+    tbl = pa.table({"txid": tx, "height": pa.array((800000 + np.arange(rows_file) // 3000).astype(np.int32)), "tweak_key": tw, "outputs": outs})
+    d = tempfile.mkdtemp(prefix="cudasp_bench_")
+    path = os.path.join(d, "t.parquet")
+    pq.write_table(tbl, path, row_group_size=122880, compression="NONE")
+    return T, path, d, time.perf_counter() - t0
+
+
+def reference_sql_run(exe, synth, T, rows, L, batch, steps, warmup):
+    """The reference's OWN DuckDB extension (oracle/_ref/duckdb_ref: src/cudasp_extension.cu + src/cudasp_gpu.cu + gECC, unmodified,
+    in the vendored DuckDB v1.4.1) through its own public API: the SQL of its README (README.md:100-124) on a Parquet file of the
+    table, PRAGMA threads = host cores; it spreads its worker threads over every visible GPU itself (src/cudasp_extension.cu:516-532).
+    -> (rows/s, ms per step, seconds per step list)"""
+    _, path, d, _ = write_parquet_table(synth, rows, L, 0.5, batch, table=T)
+    try:
+        lab = "[" + ", ".join(sql_blob(l) for l in T["labels"]) + "]" + ("" if T["labels"] else "::BLOB[]")
+        scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM read_parquet('%s')), %s, %s, %s, batch_size := %d);" % (
+            path, sql_blob(T["sk"]), sql_blob(T["spend"]), lab, batch)
+        sql = "PRAGMA threads=%d;\n.timer on\n" % (os.cpu_count() or 1) + (scan + "\n") * (warmup + steps)
+        p = subprocess.run([exe, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=3000)
+        lines = [l for l in p.stdout.strip().splitlines() if l]
+        times = [float(l.split("real")[1].split()[0]) for l in lines if l.startswith("Run Time")]
+        counts = [int(l) for l in lines if not l.startswith("Run Time")]
+        assert p.returncode == 0 and len(times) == warmup + steps, (p.returncode, p.stderr[-400:])
+        assert all(c == len(T["expected"]) for c in counts), "the reference's match count differs from the planted matches: %r" % counts[:3]
+        ts = times[warmup:]
+        return rows / (sum(ts) / len(ts)), 1e3 * sum(ts) / len(ts), ts
+    finally:
+        try:
+            os.remove(path)
+            os.rmdir(d)
+        except OSError:
+            pass
 
 
 def one_handle_leg(M, T, rows, n_dev, batch, steps):
@@ -270,28 +349,9 @@ def duckdb_leg(synth, rows_file, replicate, labels, geom_p, batch, n_dev):
     exe = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "duckdb_ext", "bin", "duckdb")
     if not os.path.exists(exe):
         return {"unavailable": "duckdb_ext/bin/duckdb not built (tools/build_duckdb.sh needs the vendored DuckDB source)"}
-    import tempfile
-    import pyarrow as pa
-    import pyarrow.parquet as pq
-    t0 = time.perf_counter()
-    seed = 352005 if labels == 16 else 352003
-    T = synth.make_table(rows_file, seed, n_labels=labels, n_base=1000 if labels == 16 else 100, n_per_label=100 if labels else 0,
-                         batch_rows=batch, geom_p=geom_p, max_extra=63 if geom_p < 0.5 else 15)
-    off = T["offsets"].astype(np.int64)
-    tw = pa.FixedSizeBinaryArray.from_buffers(pa.binary(64), rows_file, [None, pa.py_buffer(T["tweaks"].tobytes())]).cast(pa.binary())
-    txid = np.zeros((rows_file, 32), np.uint8)
-    txid[:, :8] = np.arange(rows_file, dtype=np.uint64).view(np.uint8).reshape(rows_file, 8)
-    tx = pa.FixedSizeBinaryArray.from_buffers(pa.binary(32), rows_file, [None, pa.py_buffer(txid.tobytes())]).cast(pa.binary())
-    outs = pa.ListArray.from_arrays(pa.array(off.astype(np.int32), pa.int32()), pa.array(T["outputs"], pa.int64()))
-    tbl = pa.table({"txid": tx, "height": pa.array((800000 + np.arange(rows_file) // 3000).astype(np.int32)), "tweak_key": tw, "outputs": outs})
-    d = tempfile.mkdtemp(prefix="cudasp_bench_")
-    path = os.path.join(d, "t.parquet")
-    pq.write_table(tbl, path, row_group_size=122880, compression="NONE")
-    del tbl, tw, tx, outs, txid
-    gen_s = time.perf_counter() - t0
+    T, path, d, gen_s = write_parquet_table(synth, rows_file, labels, geom_p, batch)
 
-    def blob(b):
-        return "'" + "".join("\\x%02x" % c for c in b) + "'::BLOB"
+    blob = sql_blob
     lab = "[" + ", ".join(blob(l) for l in T["labels"]) + "]" + ("" if T["labels"] else "::BLOB[]")
     src = "read_parquet([%s])" % ", ".join(["'%s'" % path] * replicate)
     threads = os.cpu_count() or 1
@@ -303,6 +363,7 @@ def duckdb_leg(synth, rows_file, replicate, labels, geom_p, batch, n_dev):
     scan_t = scan.replace(src, "tweak")
     sql = ("PRAGMA threads=%d;\n.timer on\n%s\n%s\n%s\n%s\n.timer off\nCREATE TABLE tweak AS SELECT txid, height, tweak_key, outputs FROM %s;\n"
            ".timer on\n%s\n%s\n%s\n" % (threads, scan, scan, scan, plain, src, scan_t, scan_t, plain.replace(src, "tweak")))
+    gen_s = round(gen_s, 1)
     try:
         p = subprocess.run([exe, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1200)
         lines = [l for l in p.stdout.strip().splitlines() if l]
@@ -321,7 +382,7 @@ def duckdb_leg(synth, rows_file, replicate, labels, geom_p, batch, n_dev):
                 "from_parquet": {"value": rows / warm, "unit": "rows/s", "source": "read_parquet() inside the query", "scan_s_warm": warm,
                                  "scan_s_first": times[0], "plain_read_all_columns_s": times[3]},
                 "rows": rows, "labels": labels, "mean_outputs_per_row": float(len(T["outputs"])) / rows_file,
-                "devices": n_dev, "duckdb_threads": threads, "matches_expected": want, "match_count_ok": True, "file_rows": rows_file, "read_times": replicate, "table_gen_s": round(gen_s, 1),
+                "devices": n_dev, "duckdb_threads": threads, "matches_expected": want, "match_count_ok": True, "file_rows": rows_file, "read_times": replicate, "table_gen_s": gen_s,
                 "query": "SELECT count(*) FROM cudasp_scan((SELECT txid,height,tweak_key,outputs FROM read_parquet(...)), sk, spend, labels, batch_size := %d)" % batch}
     finally:
         try:
@@ -534,7 +595,7 @@ def main():
                            "sample": "%d rows of the same table, oracle/ref_scan.py (pure Python, as the reference's verifier scripts), %.1f s" % (n_py, dtp)}
             except Exception as ex:
                 py_base = {"unavailable": repr(ex)[:200]}
-        gecc = None
+        gecc = gecc_sql = None
         if world == 1:
             try:
                 from oracle import gecc_ref as GR
@@ -548,6 +609,16 @@ def main():
                                       "B200, host buffers in / flags out, %.3f s" % (nref, dt), "flags_equal_planted": ok}
             except Exception as ex:   # the baseline is optional; the product line must still print
                 gecc = {"unavailable": repr(ex)[:200]}
+            # ... and through the reference's own DuckDB extension: the same SQL as the `duckdb` leg, the same table
+            ref_exe = os.path.join(ROOT, "oracle", "_ref", "duckdb_ref")
+            if os.path.exists(ref_exe) and not args.no_legs:
+                try:
+                    v, ms, _ = reference_sql_run(ref_exe, synth, T, rows, L, args.batch, 1, 1)
+                    gecc_sql = {"value": v, "unit": "rows/s", "kind": "reference", "ms_per_query": ms,
+                                "sample": "the unmodified reference DuckDB extension (oracle/_ref/duckdb_ref) on the same %d-row table as Parquet, its README's "
+                                          "SQL, %d DuckDB threads, same B200; match count equal to the planted matches" % (rows, cores)}
+                except Exception as ex:      # noqa: BLE001
+                    gecc_sql = {"unavailable": repr(ex)[:200]}
         line = {"metric": metric_name(L), "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u32", "data": "synthetic", "config": config, "clocks": clocks,
@@ -563,7 +634,7 @@ def main():
                              "hbm_gbs_per_gpu": (value / world) * (64 + 8 * float(T["outputs"].shape[0]) / rows + 4) / 1e9},
                 "cpu_baseline": {"value": cpu_rate, "unit": "rows/s", "cores": cores, "kind": "port",
                                  "sample": "%d rows of the same table, oracle/cudasp_oracle.c, %d pthreads, %.1f s" % (cpu_n, cores, cpu_dt)},
-                "cpu_openssl": cpu_ossl, "python_baseline": py_base, "gecc_baseline": gecc,
+                "cpu_openssl": cpu_ossl, "python_baseline": py_base, "gecc_baseline": gecc, "gecc_sql_baseline": gecc_sql,
                 "one_handle": one_handle, "duckdb": duck}
         emit(line)
 

@@ -24,3 +24,4 @@ if [ -x oracle/_ref/duckdb_ref ]; then
 fi
 timeout 900 python bench.py --steps 5 --warmup 3 > $O/bench_n1.json 2> $O/bench_n1.err; tail -c 900 $O/bench_n1.json
 ls -la $O
+timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_reference_arm.json 2> $O/bench_reference_arm.err; tail -c 700 $O/bench_reference_arm.json
