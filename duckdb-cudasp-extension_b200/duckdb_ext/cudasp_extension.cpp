@@ -139,9 +139,9 @@ struct CudaspScanState : public GlobalTableFunctionState {
 	std::mutex inflight_lock;
 	std::unordered_map<uint64_t, unique_ptr<InFlightBatch>> inflight;
 	vector<unique_ptr<InFlightBatch>> meta_pool;  // collected batches' host columns, recycled (their vectors keep capacity)
-	// The first batches of a query are cut short (1/8, 1/4, 1/2 of batch_size, one round of devices each) so that the
-	// GPUs start while the workers are still filling their first full batch; batch_size stays the maximum.
-	std::atomic<uint32_t> batches_started {0};
+	// Every worker's first batches are cut short (1/8, 1/4, 1/2 of the steady size, see EnsureSlot) so that the GPUs start
+	// while the workers are still filling their first full batch; batch_size stays the maximum.
+	std::atomic<uint32_t> batches_started {0};  // statistics only
 	uint32_t n_devices = 1;
 	uint32_t batch_size = 300000;
 	// Every worker fills its own batch, so threads x batch / 2 rows are still on the host when the input ends and the
@@ -177,7 +177,7 @@ struct CudaspScanLocalState : public LocalTableFunctionState {
 	uint32_t rows = 0;
 	uint64_t n_outputs = 0;
 	uint32_t key_bytes = 64;   // key format of the batch being filled
-	uint32_t batch_limit = 0;  // rows after which the batch being filled is submitted (<= batch_size, see batches_started)
+	uint32_t batch_limit = 0;  // rows after which the batch being filled is submitted (<= batch_size, see EnsureSlot)
 	unique_ptr<InFlightBatch> meta;
 };
 
@@ -448,8 +448,14 @@ static void EnsureSlot(CudaspScanState &state, CudaspScanLocalState &local) {
 	if (!local.meta) {
 		local.meta = make_uniq<InFlightBatch>();
 	}
-	const uint32_t round = state.batches_started++ / state.n_devices;
-	local.batch_limit = MaxValue<uint32_t>(MinValue<uint32_t>(state.steady_limit, 16384u), state.steady_limit >> (round < 3 ? 3 - round : 0));
+	// Every worker ramps its OWN batches up: 1/8, 1/4, 1/2 of the steady size (not below 16 K rows), then full.  The GPUs start
+	// after a few milliseconds of input instead of after a worker's first full batch, and a table that is small against
+	// threads x batch (config C2: 1 M rows on 16 workers) is mostly scanned by the time its last row has been decoded, instead
+	// of arriving as one partial batch per worker in Final.  Small batches of different workers run side by side on their
+	// slots' streams.  (Round 1 ramped only the first batches of the whole query: one round of devices per size.)
+	const uint32_t k = (uint32_t)MinValue<uint64_t>(local.batches++, 3);
+	local.batch_limit = MaxValue<uint32_t>(MinValue<uint32_t>(state.steady_limit, 16384u), state.steady_limit >> (3 - k));
+	state.batches_started++;
 	local.meta->txid_bytes.Reserve((size_t)local.batch_limit * TXID_SIZE);
 	local.meta->heights.Reserve(local.batch_limit);
 	local.meta->tweak_keys = local.slot.tweak_keys;
