@@ -238,3 +238,20 @@ def test_malformed_offsets_are_refused(M):
         assert L.cudasp_wait(q.handle, C.byref(r)) == 1
         assert [r.match_ids[i] for i in range(r.n_matches)] == T["expected"].tolist()
         assert L.cudasp_release_result(q.handle, C.byref(r)) == 0
+
+
+def test_scan_batch_staging_threads_and_counters(M):
+    """cudasp_scan_batch_mt: the match set does not depend on the number of staging threads (pieces are taken from one list by
+    whichever thread is free, results merged and sorted), and the transfer counters account for every byte handed to the copies."""
+    rows = 700000                                    # > 4 pieces of two ladder waves, ragged tail
+    T = synth.make_table(rows, 31337, n_labels=1, n_base=60, n_per_label=30, batch_rows=300000)
+    with M.Query(T["sk"], T["spend"], T["labels"], devices=[0], batch_rows=300000) as q:
+        for th in (1, 3, 8, 0):
+            h0, d0 = q.transfer_bytes()
+            ids = q.scan_batch(T["tweaks"], T["outputs"], T["offsets"], host_threads=th)
+            assert np.array_equal(ids, T["expected"]), th
+            h1, d1 = q.transfer_bytes()
+            # keys + outputs + one offsets array (rows + 1 entries) per piece
+            assert h1 - h0 >= rows * 64 + 8 * int(T["offsets"][-1]) + 4 * (rows + 1)
+            assert h1 - h0 <= rows * 64 + 8 * int(T["offsets"][-1]) + 4 * (rows + 64)
+            assert 0 < d1 - d0 < 64 * 4 * 1025
