@@ -26,6 +26,13 @@
 
 #include "../../include/cudasp.h"
 
+#if defined(__SSE2__) && !defined(CUDASP_NO_STREAMING_STORES)
+#include <emmintrin.h>
+#define CUDASP_NT 1
+#else
+#define CUDASP_NT 0
+#endif
+
 namespace duckdb {
 
 namespace {
@@ -46,6 +53,28 @@ struct CudaspScanBindData : public TableFunctionData {
 	bool emit_early = false;  // emit_early := true (extension): matches leave during Execute, not only in Final
 	bool details = false;  // details := true (extension): one result row per found output, + k, output_index, label_index, t_k
 };
+
+// The staged keys (pinned slot) and the kept txids are written once and not read by this CPU again -- the GPU's copy engine reads the
+// slot, a txid is read back only for the handful of rows that match -- so they are written with streaming (non-temporal) stores: no
+// read-for-ownership of the destination line, no cache pollution.  With 32 workers feeding 8 GPUs the extension moves ~130 B per row
+// each way, and host memory bandwidth is what the workers share.  dst must be 16-byte aligned; FenceStreamingStores() before the
+// data is handed on.
+template <idx_t BYTES>
+static inline void CopyStreaming(void *dst, const void *src) {
+	static_assert(BYTES % 16 == 0, "whole 16-byte blocks");
+#if CUDASP_NT
+	for (idx_t i = 0; i < BYTES / 16; i++) {
+		_mm_stream_si128(reinterpret_cast<__m128i *>(dst) + i, _mm_loadu_si128(reinterpret_cast<const __m128i *>(src) + i));
+	}
+#else
+	memcpy(dst, src, BYTES);
+#endif
+}
+static inline void FenceStreamingStores() {
+#if CUDASP_NT
+	_mm_sfence();
+#endif
+}
 
 // Growable byte buffer that does NOT value-initialise what it grows by (vector::resize would write every txid byte twice)
 // and keeps its capacity when a batch's metadata is recycled.
@@ -170,6 +199,7 @@ struct CudaspScanLocalState : public LocalTableFunctionState {
 	bool have_slot = false;
 	bool input_consumed = false;  // emit_early: the current input chunk is already staged (we are being re-called for output)
 	double accumulate_s = 0, first_input = 0;
+	double slot_wait_s = 0;  // trace: time EnsureSlot spent waiting for the GPUs (every slot busy)
 	uint64_t rows_seen = 0, batches = 0;
 	uint32_t chunks_since_poll = 0;
 	uint64_t rows_fast = 0;  // rows staged by AccumulateInput's column-wise fast path (trace)
@@ -420,6 +450,16 @@ static void EnsureSlot(CudaspScanState &state, CudaspScanLocalState &local) {
 		}
 		// every slot is busy: help by collecting the oldest batch in flight (this frees a slot); if nothing is in
 		// flight the slots are all being filled by other workers -- block until one of them is recycled.
+		const double t_wait = TraceOn() ? NowSec() : 0;
+		struct WaitTimer {
+			CudaspScanLocalState &l;
+			double t0;
+			~WaitTimer() {
+				if (TraceOn()) {
+					l.slot_wait_s += NowSec() - t0;
+				}
+			}
+		} wait_timer {local, t_wait};
 		cudasp_result r;
 		rc = cudasp_wait(state.query, &r);
 		if (rc < 0) {
@@ -472,6 +512,7 @@ static void SubmitSlot(CudaspScanState &state, CudaspScanLocalState &local) {
 		std::lock_guard<std::mutex> guard(state.inflight_lock);
 		state.inflight[tag] = std::move(local.meta);
 	}
+	FenceStreamingStores();
 	const int fmt = local.key_bytes == SEC1_SIZE ? CUDASP_KEYS_SEC1_33 : CUDASP_KEYS_XY64;
 	if (cudasp_submit_slot_fmt(state.query, &local.slot, local.rows, local.n_outputs, tag, fmt) != CUDASP_OK) {
 		ThrowGpu(state, "cudasp_submit_slot");
@@ -575,7 +616,7 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 				if (tw.GetSize() != POINT_SIZE) {
 					break;
 				}
-				memcpy(kdst + m * POINT_SIZE, tw.GetData(), POINT_SIZE);
+				CopyStreaming<POINT_SIZE>(kdst + m * POINT_SIZE, tw.GetData());
 			}
 		} else {
 			for (m = 0; m < n; m++) {
@@ -610,7 +651,7 @@ static void AccumulateInput(CudaspScanState &state, CudaspScanLocalState &local,
 				if (tx.GetSize() != TXID_SIZE) {
 					break;
 				}
-				memcpy(tdst + m * TXID_SIZE, tx.GetData(), TXID_SIZE);
+				CopyStreaming<TXID_SIZE>(tdst + m * TXID_SIZE, tx.GetData());
 			}
 			if (m < n) {  // an odd-sized txid: switch this batch to the explicit index and append the rest one by one
 				meta.txid_bytes.Truncate((size_t)(row0 + m) * TXID_SIZE);
@@ -772,8 +813,8 @@ static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &cont
 
 	if (!local.finalized) {
 		if (TraceOn()) {
-			fprintf(stderr, "[cudasp] worker: %llu rows (%llu column-wise), accumulate+drain %.3f s, span %.3f s\n",
-			        (unsigned long long)local.rows_seen, (unsigned long long)local.rows_fast, local.accumulate_s,
+			fprintf(stderr, "[cudasp] worker: %llu rows (%llu column-wise), accumulate+drain %.3f s (of which waiting for a slot %.3f s), span %.3f s\n",
+			        (unsigned long long)local.rows_seen, (unsigned long long)local.rows_fast, local.accumulate_s, local.slot_wait_s,
 			        local.rows_seen ? NowSec() - local.first_input : 0.0);
 		}
 		SubmitSlot(state, local);
