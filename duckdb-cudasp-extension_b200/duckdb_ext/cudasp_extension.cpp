@@ -25,6 +25,7 @@
 #include <unordered_map>
 
 #include "../../include/cudasp.h"
+#include "../../include/cudasp_parquet.h"
 
 #if defined(__SSE2__) && !defined(CUDASP_NO_STREAMING_STORES)
 #include <emmintrin.h>
@@ -228,33 +229,27 @@ double NowSec() {
 }  // namespace
 
 // ------------------------------------------------------------------------------------------ bind
-// Same checks, same order, same messages as the reference's CudaspScanBind (:420-509).
-static unique_ptr<FunctionData> CudaspScanBind(ClientContext &context, TableFunctionBindInput &input,
-                                               vector<LogicalType> &return_types, vector<string> &names) {
-	if (input.inputs.size() != 4) {
-		throw InvalidInputException("cudasp_scan requires 4 arguments: TABLE, scan_private_key BLOB, spend_public_key "
-		                            "BLOB, and label_keys LIST[BLOB]");
-	}
-	auto result = make_uniq<CudaspScanBindData>();
-
+// The key arguments (positions 1..3) and batch_size, shared by cudasp_scan and cudasp_scan_parquet: same checks, same order, same
+// messages as the reference's CudaspScanBind (:423-487).
+static void BindKeys(TableFunctionBindInput &input, CudaspScanBindData &result) {
 	auto &sk = input.inputs[1];
 	if (sk.type().id() != LogicalTypeId::BLOB) {
 		throw InvalidInputException("Second argument must be a BLOB (32-byte scan_private_key)");
 	}
-	result->scan_private_key = StringValue::Get(sk);
-	if (result->scan_private_key.size() != SCALAR_SIZE) {
+	result.scan_private_key = StringValue::Get(sk);
+	if (result.scan_private_key.size() != SCALAR_SIZE) {
 		throw InvalidInputException("scan_private_key must be exactly 32 bytes, got %llu bytes",
-		                            (uint64_t)result->scan_private_key.size());
+		                            (uint64_t)result.scan_private_key.size());
 	}
 
 	auto &spend = input.inputs[2];
 	if (spend.type().id() != LogicalTypeId::BLOB) {
 		throw InvalidInputException("Third argument must be a BLOB (64-byte spend_public_key)");
 	}
-	result->spend_public_key = StringValue::Get(spend);
-	if (result->spend_public_key.size() != POINT_SIZE) {
+	result.spend_public_key = StringValue::Get(spend);
+	if (result.spend_public_key.size() != POINT_SIZE) {
 		throw InvalidInputException("spend_public_key must be exactly 64 bytes, got %llu bytes",
-		                            (uint64_t)result->spend_public_key.size());
+		                            (uint64_t)result.spend_public_key.size());
 	}
 
 	auto &labels = input.inputs[3];
@@ -270,11 +265,11 @@ static unique_ptr<FunctionData> CudaspScanBind(ClientContext &context, TableFunc
 			if (key.size() != POINT_SIZE) {
 				throw InvalidInputException("Each label key must be exactly 64 bytes, got %llu bytes", (uint64_t)key.size());
 			}
-			result->label_keys += key;
-			result->n_labels++;
+			result.label_keys += key;
+			result.n_labels++;
 		}
 	}
-	if (result->n_labels > CUDASP_MAX_LABELS) {
+	if (result.n_labels > CUDASP_MAX_LABELS) {
 		throw InvalidInputException("cudasp_scan supports at most %llu label keys", (uint64_t)CUDASP_MAX_LABELS);
 	}
 
@@ -291,8 +286,20 @@ static unique_ptr<FunctionData> CudaspScanBind(ClientContext &context, TableFunc
 		if (v > (int64_t)MAX_BATCH) {
 			throw InvalidInputException("batch_size too large (max 10,000,000), got %lld", (long long)v);
 		}
-		result->batch_size = (idx_t)v;
+		result.batch_size = (idx_t)v;
 	}
+
+}
+
+// Same checks, same order, same messages as the reference's CudaspScanBind (:420-509).
+static unique_ptr<FunctionData> CudaspScanBind(ClientContext &context, TableFunctionBindInput &input,
+                                               vector<LogicalType> &return_types, vector<string> &names) {
+	if (input.inputs.size() != 4) {
+		throw InvalidInputException("cudasp_scan requires 4 arguments: TABLE, scan_private_key BLOB, spend_public_key "
+		                            "BLOB, and label_keys LIST[BLOB]");
+	}
+	auto result = make_uniq<CudaspScanBindData>();
+	BindKeys(input, *result);
 
 	auto ee = input.named_parameters.find("emit_early");
 	if (ee != input.named_parameters.end()) {
@@ -844,6 +851,133 @@ static OperatorFinalizeResultType CudaspScanFinalFunction(ExecutionContext &cont
 	                                                         : OperatorFinalizeResultType::FINISHED;
 }
 
+// ------------------------------------------------------------------------------------------ cudasp_scan_parquet
+// Sibling of cudasp_scan for tables that live in Parquet files (no counterpart in the reference, whose users go
+// through read_parquet + AccumulateInput, README.md:100-110):
+//     SELECT * FROM cudasp_scan_parquet('tweaks.parquet' | ['a.parquet', ...], scan_private_key, spend_public_key, label_keys
+//                                       [, batch_size := N] [, threads := T])
+// Same key arguments, checks, error texts and result columns as cudasp_scan.  The pages are decoded by the C-ABI library itself
+// (include/cudasp_parquet.h) straight into pinned staging, one row group per host thread in flight, without becoming DuckDB vectors.
+// Files outside that reader's subset (codecs other than none / Snappy, other column shapes) are refused with a message that names
+// the feature and points at cudasp_scan((SELECT ... FROM read_parquet(...)), ...), which reads anything DuckDB can read.
+struct CudaspParquetBindData : public CudaspScanBindData {
+	vector<string> paths;
+	int64_t threads = 0;
+};
+
+struct CudaspParquetState : public GlobalTableFunctionState {
+	~CudaspParquetState() override {
+		if (result) {
+			cudasp_parquet_result_free(result);
+		}
+		if (query) {
+			cudasp_query_destroy(query);
+		}
+	}
+	idx_t MaxThreads() const override {
+		return 1;  // the library runs its own decoder threads
+	}
+	cudasp_query *query = nullptr;
+	cudasp_parquet_result *result = nullptr;
+	bool scanned = false;
+	idx_t position = 0;
+};
+
+static unique_ptr<FunctionData> CudaspParquetBind(ClientContext &context, TableFunctionBindInput &input,
+                                                  vector<LogicalType> &return_types, vector<string> &names) {
+	if (input.inputs.size() != 4) {
+		throw InvalidInputException("cudasp_scan_parquet requires 4 arguments: path VARCHAR or LIST[VARCHAR], scan_private_key "
+		                            "BLOB, spend_public_key BLOB, and label_keys LIST[BLOB]");
+	}
+	auto result = make_uniq<CudaspParquetBindData>();
+	auto &p = input.inputs[0];
+	if (p.IsNull()) {
+		throw InvalidInputException("First argument must be a VARCHAR path or a LIST[VARCHAR] of paths, not NULL");
+	}
+	if (p.type().id() == LogicalTypeId::VARCHAR) {
+		result->paths.push_back(StringValue::Get(p));
+	} else if (p.type().id() == LogicalTypeId::LIST) {
+		for (auto &child : ListValue::GetChildren(p)) {
+			if (child.type().id() != LogicalTypeId::VARCHAR || child.IsNull()) {
+				throw InvalidInputException("All elements of the path list must be VARCHARs");
+			}
+			result->paths.push_back(StringValue::Get(child));
+		}
+	} else {
+		throw InvalidInputException("First argument must be a VARCHAR path or a LIST[VARCHAR] of paths");
+	}
+	BindKeys(input, *result);
+	auto th = input.named_parameters.find("threads");
+	if (th != input.named_parameters.end() && !th->second.IsNull()) {
+		result->threads = th->second.GetValue<int64_t>();
+		if (result->threads < 0 || result->threads > 1024) {
+			throw InvalidInputException("threads must be between 0 and 1024, got %lld", (long long)result->threads);
+		}
+	}
+	return_types = {LogicalType::BLOB, LogicalType::INTEGER, LogicalType::BLOB};
+	names = {"txid", "height", "tweak_key"};
+	return std::move(result);
+}
+
+static unique_ptr<GlobalTableFunctionState> CudaspParquetInit(ClientContext &context, TableFunctionInitInput &input) {
+	return make_uniq<CudaspParquetState>();
+}
+
+static void CudaspParquetFunction(ClientContext &context, TableFunctionInput &data_p, DataChunk &output) {
+	auto &bind = data_p.bind_data->Cast<CudaspParquetBindData>();
+	auto &state = data_p.global_state->Cast<CudaspParquetState>();
+	if (!state.scanned) {
+		state.scanned = true;
+		int n_dev = cudasp_device_count();
+		if (n_dev <= 0) {
+			throw IOException("cudasp_scan_parquet: no CUDA device available (this extension has no CPU path)");
+		}
+		idx_t threads = bind.threads > 0 ? (idx_t)bind.threads
+		                                 : MaxValue<idx_t>(1, NumericCast<idx_t>(TaskScheduler::GetScheduler(context).NumberOfThreads()));
+		// every decoder thread has one row group in flight, staged in pieces of at most batch_size rows
+		uint32_t slots = (uint32_t)MinValue<idx_t>(64, (threads + n_dev - 1) / n_dev + 2);
+		int rc = cudasp_query_create_ex(const_data_ptr_cast(bind.scan_private_key.data()), const_data_ptr_cast(bind.spend_public_key.data()),
+		                                bind.n_labels ? const_data_ptr_cast(bind.label_keys.data()) : nullptr, bind.n_labels, nullptr, 0,
+		                                (uint32_t)bind.batch_size, 8ull * bind.batch_size, slots, &state.query);
+		if (rc != CUDASP_OK) {
+			const char *msg = cudasp_last_error(nullptr);
+			if (rc == CUDASP_ERR_KEY || rc == CUDASP_ERR_ARG) {
+				throw InvalidInputException("cudasp_scan_parquet: %s", msg ? msg : "invalid keys");
+			}
+			throw IOException("cudasp_scan_parquet: GPU initialisation failed: %s", msg ? msg : "unknown error");
+		}
+		vector<const char *> cpaths;
+		for (auto &p : bind.paths) {
+			cpaths.push_back(p.c_str());
+		}
+		rc = cudasp_scan_parquet(state.query, cpaths.data(), (int)cpaths.size(), (int)threads, &state.result);
+		if (rc != CUDASP_OK) {
+			const char *msg = cudasp_last_error(state.query);
+			if (rc == CUDASP_ERR_UNSUPPORTED) {
+				throw InvalidInputException("cudasp_scan_parquet: %s -- use cudasp_scan((SELECT txid, height, tweak_key, outputs FROM "
+				                            "read_parquet(...)), ...) for this file",
+				                            msg ? msg : "unsupported Parquet feature");
+			}
+			throw IOException("cudasp_scan_parquet: %s", msg ? msg : "scan failed");
+		}
+	}
+	const cudasp_parquet_result &r = *state.result;
+	const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, (idx_t)r.n_matches - state.position);
+	auto txid_out = FlatVector::GetData<string_t>(output.data[0]);
+	auto height_out = FlatVector::GetData<int32_t>(output.data[1]);
+	auto tweak_out = FlatVector::GetData<string_t>(output.data[2]);
+	for (idx_t i = 0; i < n; i++) {
+		const idx_t k = state.position + i;
+		txid_out[i] = StringVector::AddStringOrBlob(output.data[0], const_char_ptr_cast(r.txids + r.txid_offsets[k]),
+		                                            (idx_t)(r.txid_offsets[k + 1] - r.txid_offsets[k]));
+		height_out[i] = r.heights[k];
+		tweak_out[i] = StringVector::AddStringOrBlob(output.data[2], const_char_ptr_cast(r.tweak_keys + r.key_offsets[k]),
+		                                             (idx_t)(r.key_offsets[k + 1] - r.key_offsets[k]));
+	}
+	output.SetCardinality(n);
+	state.position += n;
+}
+
 // ------------------------------------------------------------------------------------------ registration
 static void LoadInternal(ExtensionLoader &loader) {
 	TableFunction func("cudasp_scan",
@@ -855,6 +989,14 @@ static void LoadInternal(ExtensionLoader &loader) {
 	func.named_parameters["details"] = LogicalType::BOOLEAN;
 	func.named_parameters["emit_early"] = LogicalType::BOOLEAN;
 	loader.RegisterFunction(func);
+
+	for (auto &path_type : {LogicalType(LogicalType::VARCHAR), LogicalType::LIST(LogicalType::VARCHAR)}) {
+		TableFunction pfunc("cudasp_scan_parquet", {path_type, LogicalType::BLOB, LogicalType::BLOB, LogicalType::LIST(LogicalType::BLOB)},
+		                    CudaspParquetFunction, CudaspParquetBind, CudaspParquetInit);
+		pfunc.named_parameters["batch_size"] = LogicalType::INTEGER;
+		pfunc.named_parameters["threads"] = LogicalType::INTEGER;
+		loader.RegisterFunction(pfunc);
+	}
 }
 
 void CudaspExtension::Load(ExtensionLoader &loader) {

@@ -224,3 +224,10 @@ int cudasp_release_result(cudasp_query *q, const cudasp_result *r) {
   return CUDASP_OK;
 }
 }  // extern "C"
+
+// cudasp_scan_parquet (include/cudasp_parquet.h) needs the real library's page decoders and staging: not in this double
+#include "../../include/cudasp_parquet.h"
+extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *, int, int, cudasp_parquet_result **) {
+  return fail(q, CUDASP_ERR_UNSUPPORTED, "mock: cudasp_scan_parquet needs the GPU build");
+}
+extern "C" void cudasp_parquet_result_free(cudasp_parquet_result *) {}

@@ -41,6 +41,15 @@ def test_arrow_exports_match_header(M):
     assert "staging" not in syms
 
 
+def test_parquet_exports_match_header(M):
+    hdr = open(os.path.join(ROOT, "include", "cudasp_parquet.h")).read()
+    declared = set(re.findall(r"\b(cudasp_[a-z_]+)\s*\(", hdr)) - {"cudasp_last_error", "cudasp_scan"}      # mentioned in comments
+    assert declared == set(M.PARQUET_EXPORTS), declared ^ set(M.PARQUET_EXPORTS)
+    L = M.lib()
+    for name in declared:
+        assert getattr(L, name) is not None
+
+
 def test_no_cpu_fallback(M):
     import torch
     if torch.cuda.is_available():

@@ -153,3 +153,17 @@ def test_emit_early_and_bind_errors(mock):
     rc, out, err = run(mock, make(10) + "SELECT * FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM src), repeat('\\x00',32)::BLOB, "
                        "repeat('\\x02',64)::BLOB, []::BLOB[]);")
     assert rc != 0 and "Invalid Input Error" in err and "all-zero scan key" in err       # CUDASP_ERR_KEY -> InvalidInputException
+
+
+def test_cudasp_scan_parquet_bind_and_refusal(mock, tmp_path):
+    """The Parquet sibling: same key checks and texts as cudasp_scan; the C ABI's CUDASP_ERR_UNSUPPORTED becomes an error that points
+    at cudasp_scan over read_parquet (the double refuses every file; the decoders themselves are tested in test_parquet_ingest.py)."""
+    rc, out, err = run(mock, "SELECT * FROM cudasp_scan_parquet('x.parquet', repeat('\\x01',31)::BLOB, repeat('\\x02',64)::BLOB, []::BLOB[]);")
+    assert rc != 0 and "scan_private_key must be exactly 32 bytes, got 31 bytes" in err
+    rc, out, err = run(mock, "SELECT * FROM cudasp_scan_parquet(42, repeat('\\x01',32)::BLOB, repeat('\\x02',64)::BLOB, []::BLOB[]);")
+    assert rc != 0
+    rc, out, err = run(mock, "SELECT * FROM cudasp_scan_parquet(['a.parquet', 'b.parquet'], repeat('\\x01',32)::BLOB, repeat('\\x02',64)::BLOB, "
+                       "[repeat('\\x03',63)::BLOB]);")
+    assert rc != 0 and "Each label key must be exactly 64 bytes, got 63 bytes" in err
+    rc, out, err = run(mock, "SELECT * FROM cudasp_scan_parquet('x.parquet', repeat('\\x01',32)::BLOB, repeat('\\x02',64)::BLOB, []::BLOB[], threads := 2);")
+    assert rc != 0 and "use cudasp_scan((SELECT txid, height, tweak_key, outputs FROM read_parquet(...))" in err
