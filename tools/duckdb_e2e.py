@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--compressed", action="store_true", help="store tweak_key as 33-byte SEC1 (decompressed on the GPU)")
     ap.add_argument("--details", action="store_true", help="details := true (one result row per found output)")
     ap.add_argument("--in-memory", action="store_true", help="load the table into a DuckDB table first (no Parquet decode in the timed query)")
+    ap.add_argument("--native", action="store_true", help="also time cudasp_scan_parquet(paths, ...): the library's own page decoders instead of DuckDB's read_parquet")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "both"], help="which extension runs the SQL (same file, same query)")
     a = ap.parse_args()
     import numpy as np
@@ -76,7 +77,12 @@ def main():
         scan = "SELECT count(*) FROM cudasp_scan((SELECT txid, height, tweak_key, outputs FROM %s), %s, %s, %s, batch_size := %d%s);" % (
             cur, blob(T["sk"]), blob(T["spend"]), labels, a.batch, ", details := true" if a.details else "")
         plain = "SELECT count(*), sum(height), sum(octet_length(tweak_key)), sum(len(outputs)) FROM %s;" % cur
-        sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + "SELECT current_setting('threads');\n"
+        native = ""
+        if a.native and impl == "ours" and not a.details:
+            paths = "[%s]" % ", ".join(["'%s'" % path] * a.replicate)
+            nq = "SELECT count(*) FROM cudasp_scan_parquet(%s, %s, %s, %s, batch_size := %d);" % (paths, blob(T["sk"]), blob(T["spend"]), labels, a.batch)
+            native = nq + "\n" + nq + "\n" + nq + "\n"
+        sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + native + "SELECT current_setting('threads');\n"
         p = subprocess.run([exe, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
         if os.environ.get("CUDASP_TRACE"):
             sys.stderr.write(p.stderr)
@@ -90,6 +96,9 @@ def main():
                "matches_ok": ok, "scan_s_cold": times[0] if times else None, "scan_s_warm": times[1] if len(times) > 1 else None,
                "plain_read_s": times[2] if len(times) > 2 else None, "gen_s": round(gen_s, 1),
                "rows_per_s_warm": rows / times[1] if len(times) > 1 else None, "stderr": p.stderr[-300:]}
+        if native and len(times) >= 6 and len(vals) >= 6:
+            res["native_parquet"] = {"scan_s_first": times[3], "scan_s_warm": min(times[4:6]), "rows_per_s_warm": rows / min(times[4:6]),
+                                     "matches_ok": all(int(v) == want for v in vals[3:6])}
         print(json.dumps(res))
     try:
         os.remove(path)
