@@ -12,6 +12,8 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -399,7 +401,18 @@ struct HybridDecoder {
       } else {
         const uint64_t k = std::min(n, packed_left);
         const uint32_t mask = bw == 32 ? 0xffffffffu : ((1u << bw) - 1u);
-        for (uint64_t i = 0; i < k; i++) {
+        uint64_t i = 0;
+        if (bw <= 8 && (bitpos & 7) == 0) {
+          // whole groups of 8 values = bw bytes: one 64-bit load, eight shifts (levels are 1-3 bits wide, dictionary indices of small
+          // dictionaries up to 8)
+          const uint8_t *g = p + (bitpos >> 3);
+          for (; i + 8 <= k && g + 8 <= end; i += 8, g += bw) {
+            uint64_t w;
+            memcpy(&w, g, 8);
+            for (int j = 0; j < 8; j++) out[i + j] = (uint32_t)(w >> (j * bw)) & mask;
+          }
+        }
+        for (; i < k; i++) {
           const uint64_t bit = bitpos + i * (uint64_t)bw;
           const uint8_t *q = p + (bit >> 3);
           uint64_t w = 0;
@@ -497,6 +510,12 @@ struct ChunkReader {
     if (start < 4 || c.total_compressed < 0 || (uint64_t)start + (uint64_t)c.total_compressed > f.size) corrupt("column chunk outside the file");
     p = f.data + start;
     end = p + c.total_compressed;
+    // map the chunk's pages in one call instead of one soft fault per 4 KB while decoding (Linux >= 5.14; harmless when refused)
+#ifndef MADV_POPULATE_READ
+#define MADV_POPULATE_READ 22
+#endif
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)4095;
+    madvise(reinterpret_cast<void *>(a0), (size_t)(reinterpret_cast<uintptr_t>(end) - a0), MADV_POPULATE_READ);
   }
   void load_dictionary(const PageHeader &h, const uint8_t *body) {
     if (h.encoding != E_PLAIN && h.encoding != E_PLAIN_DICT) unsupported("dictionary page encoding " + std::to_string(h.encoding));
@@ -587,9 +606,32 @@ struct Bitmap {
   }
   bool get(int64_t i) const { return bits[(size_t)i >> 3] & (1u << (i & 7)); }
 };
+struct RawBytes {             // growable, never value-initialised, keeps its capacity from row group to row group
+  uint8_t *p = nullptr;
+  size_t len = 0, cap = 0;
+  RawBytes() = default;
+  RawBytes(const RawBytes &) = delete;
+  RawBytes &operator=(const RawBytes &) = delete;
+  ~RawBytes() { free(p); }
+  uint8_t *grow(size_t n) {   // room for n more bytes; returns where they go
+    if (len + n > cap) {
+      const size_t want = std::max(len + n, cap + cap / 2 + 4096);
+      uint8_t *q = static_cast<uint8_t *>(realloc(p, want));
+      if (!q) throw std::bad_alloc();
+      p = q; cap = want;
+    }
+    uint8_t *at = p + len;
+    len += n;
+    return at;
+  }
+  size_t size() const { return len; }
+  bool empty() const { return len == 0; }
+  const uint8_t *data() const { return p; }
+  void clear() { len = 0; }
+};
 struct BlobColumn {           // binary: int32 offsets + bytes + validity
   std::vector<int32_t> offsets;
-  std::vector<uint8_t> data;
+  RawBytes data;
   Bitmap valid;
 };
 struct Int32Column {
@@ -599,8 +641,11 @@ struct Int32Column {
 struct ListColumn {           // list<int64>: int32 offsets + list validity; child values + child validity
   std::vector<int32_t> offsets;
   Bitmap valid;
-  std::vector<int64_t> values;
+  RawBytes value_bytes;       // int64 values, 8 bytes each
+  std::vector<uint32_t> null_children;   // positions of NULL elements (rare): child_valid is built from them
   Bitmap child_valid;
+  size_t n_values() const { return value_bytes.size() / 8; }
+  const int64_t *values() const { return reinterpret_cast<const int64_t *>(value_bytes.data()); }
 };
 
 // values of one page of a BYTE_ARRAY / FIXED_LEN_BYTE_ARRAY column: calls put(ptr, len) once per non-null value, in order
@@ -650,9 +695,11 @@ void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
   if (lf.max_rep != 0 || lf.max_def > 1) unsupported("column " + lf.path[0] + " is nested");
   if (lf.type == T_FLBA && cm.dict_page_offset > 0 && lf.type_length <= 0) corrupt("fixed-length column without a length");
   ChunkReader cr(f, cm, lf);
-  out.offsets.assign((size_t)rows + 1, 0);
+  out.offsets.resize((size_t)rows + 1);
+  out.offsets[0] = 0;
   out.data.clear();
-  out.data.reserve((size_t)rows * size_hint);
+  out.data.grow((size_t)rows * size_hint);
+  out.data.clear();
   out.valid.init(rows);
   int64_t row = 0;
   Page pg;
@@ -675,15 +722,28 @@ void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
       }
     }
     int64_t i = 0;      // value slot within the page
-    page_blobs(cr, pg, present, [&](const uint8_t *p, uint32_t len) {
-      if (!all_valid) {
-        while (defs[(size_t)i] == 0) { out.valid.clear(row + i); out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size(); i++; }
-      }
-      out.data.insert(out.data.end(), p, p + len);
+    if (all_valid && pg.encoding == E_PLAIN && lf.type == T_FLBA) {
+      // fixed-size values, no NULLs: the page's value area IS the column data
+      const size_t w = (size_t)lf.type_length, bytes = w * (size_t)n;
+      if (lf.type_length <= 0 || (size_t)(pg.values_end - pg.values) < bytes) corrupt("page: fixed-length values past the end");
+      const size_t base = out.data.size();
+      if (base + bytes > 0x7fffffffull) unsupported("more than 2 GiB of " + lf.path[0] + " in one row group");
+      memcpy(out.data.grow(bytes), pg.values, bytes);
+      int32_t *o = out.offsets.data() + row + 1;
+      for (int64_t k = 0; k < n; k++) o[k] = (int32_t)(base + w * (size_t)(k + 1));
+      i = n;
+    } else {
+      page_blobs(cr, pg, present, [&](const uint8_t *p, uint32_t len) {
+        if (!all_valid) {
+          while (defs[(size_t)i] == 0) { out.valid.clear(row + i); out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size(); i++; }
+        }
+        uint8_t *dst = out.data.grow(len);
+        if (len == 64) memcpy(dst, p, 64); else if (len == 32) memcpy(dst, p, 32); else memcpy(dst, p, len);
+        out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size();
+        i++;
+      });
       if (out.data.size() > 0x7fffffffull) unsupported("more than 2 GiB of " + lf.path[0] + " in one row group");
-      out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size();
-      i++;
-    });
+    }
     for (; i < n; i++) { out.valid.clear(row + i); out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size(); }   // trailing NULLs
     row += n;
   }
@@ -750,13 +810,13 @@ void decode_list_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
     d0 += r != 0;
   }
   ChunkReader cr(f, cm, lf);
-  out.offsets.assign((size_t)rows + 1, 0);
+  out.offsets.resize((size_t)rows + 1);
+  out.offsets[0] = 0;
   out.valid.init(rows);
-  out.values.clear();
-  out.values.reserve((size_t)cm.num_values);
-  out.child_valid.bits.clear();
-  std::vector<uint8_t> child_ok;          // one byte per child, packed at the end
-  child_ok.reserve((size_t)cm.num_values);
+  out.value_bytes.clear();
+  out.value_bytes.grow((size_t)std::max<int64_t>(cm.num_values, 1) * 8);
+  out.value_bytes.clear();
+  out.null_children.clear();
   int64_t row = -1;
   Page pg;
   std::vector<uint32_t> reps, defs, idx;
@@ -769,9 +829,14 @@ void decode_list_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
     r.init(pg.rep, pg.rep_end, 1);
     r.get(reps.data(), (uint64_t)n);
     d.init(pg.def, pg.def_end, def_bw);
-    d.get(defs.data(), (uint64_t)n);
-    int64_t present = 0;
-    for (int64_t i = 0; i < n; i++) present += defs[(size_t)i] == (uint32_t)lf.max_def;
+    const bool all_present = d.all_equal((uint64_t)n, (uint32_t)lf.max_def);
+    int64_t present = n;
+    if (!all_present) {
+      d.init(pg.def, pg.def_end, def_bw);
+      d.get(defs.data(), (uint64_t)n);
+      present = 0;
+      for (int64_t i = 0; i < n; i++) present += defs[(size_t)i] == (uint32_t)lf.max_def;
+    }
     const uint8_t *q = pg.values;
     const bool dict = pg.encoding == E_RLE_DICT || pg.encoding == E_PLAIN_DICT;
     if (dict) {
@@ -782,16 +847,34 @@ void decode_list_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
         HybridDecoder ix;
         ix.init(q + 1, pg.values_end, q[0]);
         ix.get(idx.data(), (uint64_t)present);
+        for (int64_t k = 0; k < present; k++) if (idx[(size_t)k] >= (uint32_t)cr.dict.n) corrupt("dictionary index out of range");
       }
     } else if (pg.encoding == E_PLAIN) {
       if ((int64_t)(pg.values_end - q) < 8 * present) corrupt("page: INT64 values past the end");
     } else {
       unsupported("value encoding " + std::to_string(pg.encoding) + " of column " + lf.path[0]);
     }
+    if (out.n_values() + (size_t)n > 0x7fffffffull) unsupported("more than 2^31 outputs in one row group");
+    if (present == n) {
+      // every level entry is a value (no NULL list, empty list or NULL element on this page): values are copied in one go,
+      // the repetition levels only say where rows start
+      const size_t base = out.n_values();
+      uint8_t *dst = out.value_bytes.grow((size_t)n * 8);
+      if (dict) { for (int64_t k = 0; k < n; k++) memcpy(dst + 8 * k, cr.dict.data + 8 * (size_t)idx[(size_t)k], 8); }
+      else memcpy(dst, q, (size_t)n * 8);
+      for (int64_t i = 0; i < n; i++) {
+        if (reps[(size_t)i] == 0) {
+          if (row >= 0) out.offsets[(size_t)row + 1] = (int32_t)(base + (size_t)i);
+          if (++row >= rows) corrupt("column " + lf.path[0] + ": more rows than the row group has");
+        }
+      }
+      if (row < 0) corrupt("column " + lf.path[0] + ": the row group starts inside a row");
+      continue;
+    }
     int64_t k = 0;
     for (int64_t i = 0; i < n; i++) {
       if (reps[(size_t)i] == 0) {
-        if (row >= 0) out.offsets[(size_t)row + 1] = (int32_t)out.values.size();
+        if (row >= 0) out.offsets[(size_t)row + 1] = (int32_t)out.n_values();
         if (++row >= rows) corrupt("column " + lf.path[0] + ": more rows than the row group has");
       } else if (row < 0) {
         corrupt("column " + lf.path[0] + ": the row group starts inside a row");
@@ -801,25 +884,22 @@ void decode_list_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
       if (dl == d0) continue;                                  // empty list
       int64_t v = 0;
       if (dl == lf.max_def) {
-        if (dict) {
-          if (idx[(size_t)k] >= (uint32_t)cr.dict.n) corrupt("dictionary index out of range");
-          memcpy(&v, cr.dict.data + 8 * (size_t)idx[(size_t)k], 8);
-        } else {
-          memcpy(&v, q + 8 * k, 8);
-        }
+        if (dict) memcpy(&v, cr.dict.data + 8 * (size_t)idx[(size_t)k], 8);
+        else memcpy(&v, q + 8 * k, 8);
         k++;
-        child_ok.push_back(1);
       } else {
-        child_ok.push_back(0);                                 // NULL element
+        out.null_children.push_back((uint32_t)out.n_values());  // NULL element
       }
-      out.values.push_back(v);
-      if (out.values.size() > 0x7fffffffull) unsupported("more than 2^31 outputs in one row group");
+      memcpy(out.value_bytes.grow(8), &v, 8);
     }
   }
-  if (row >= 0) out.offsets[(size_t)row + 1] = (int32_t)out.values.size();
+  if (row >= 0) out.offsets[(size_t)row + 1] = (int32_t)out.n_values();
   if (row + 1 != rows) corrupt("column " + lf.path[0] + ": fewer rows than the row group has");
-  out.child_valid.init((int64_t)child_ok.size());
-  for (size_t i = 0; i < child_ok.size(); i++) if (!child_ok[i]) out.child_valid.clear((int64_t)i);
+  out.child_valid.nulls = 0;
+  if (!out.null_children.empty()) {
+    out.child_valid.init((int64_t)out.n_values());
+    for (uint32_t pos : out.null_children) out.child_valid.clear((int64_t)pos);
+  }
 }
 
 }  // namespace
@@ -856,6 +936,29 @@ ColumnMap map_columns(const FileMeta &m) {
   return c;
 }
 
+// the four columns have the shapes the decoders handle: checked when the file is opened, before any row is scanned
+void validate_columns(const FileMeta &m, const ColumnMap &c) {
+  auto blob = [&](int l) {
+    const Leaf &lf = m.leaves[(size_t)l];
+    if (lf.type != T_BYTE_ARRAY && lf.type != T_FLBA) unsupported("column " + lf.path[0] + " is not BYTE_ARRAY / FIXED_LEN_BYTE_ARRAY");
+    if (lf.max_rep != 0 || lf.max_def > 1) unsupported("column " + lf.path[0] + " is nested");
+  };
+  blob(c.txid);
+  blob(c.tweak);
+  const Leaf &h = m.leaves[(size_t)c.height];
+  if (h.type != T_INT32) unsupported("column " + h.path[0] + " is not INT32");
+  if (h.max_rep != 0 || h.max_def > 1) unsupported("column " + h.path[0] + " is nested");
+  const Leaf &o = m.leaves[(size_t)c.outputs];
+  if (o.type != T_INT64) unsupported("column " + o.path[0] + " does not hold INT64 values");
+  if (o.max_rep != 1) unsupported("column " + o.path[0] + " is not a one-level list");
+  for (const RowGroupMeta &g : m.row_groups)
+    for (int l : {c.txid, c.height, c.tweak, c.outputs}) {
+      const int codec = g.cols[(size_t)l].codec;
+      if (codec != C_UNCOMPRESSED && codec != C_SNAPPY)
+        unsupported("compression codec " + std::to_string(codec) + " (only uncompressed and Snappy pages are decoded)");
+    }
+}
+
 struct Match {
   uint32_t file;
   uint64_t row;
@@ -870,23 +973,37 @@ struct OpenFile {
   std::vector<int64_t> row_base;   // first row of every row group
 };
 
+// CUDASP_TRACE: seconds spent per stage, summed over threads, printed once per cudasp_scan_parquet call
+struct StageClock {
+  std::atomic<uint64_t> ns[6];
+  StageClock() { for (auto &x : ns) x = 0; }
+};
+StageClock g_clock;
+inline uint64_t now_ns() { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
 // one row group: decode, hand to the Arrow ingest, keep what matched
-int scan_row_group(cudasp_query *q, const OpenFile &of, uint32_t file_index, size_t g, std::vector<Match> &matches) {
+struct Scratch {               // one per decoder thread: the decoded columns of the row group in hand, buffers reused from one to the next
+  BlobColumn txid, key;
+  Int32Column height;
+  ListColumn outs;
+  std::vector<uint64_t> ids;
+};
+int scan_row_group(cudasp_query *q, const OpenFile &of, uint32_t file_index, size_t g, std::vector<Match> &matches, Scratch &sc) {
   const RowGroupMeta &rg = of.meta.row_groups[g];
   const int64_t rows = rg.num_rows;
   if (rows == 0) return 0;
   if (rows > 0x7fffffff) unsupported("more than 2^31 rows in one row group");
-  BlobColumn txid, key;
-  Int32Column height;
-  ListColumn outs;
+  BlobColumn &txid = sc.txid, &key = sc.key;
+  Int32Column &height = sc.height;
+  ListColumn &outs = sc.outs;
+  uint64_t t0 = now_ns(), t1;
   decode_blob_column(of.map, rg.cols[(size_t)of.cols.tweak], of.meta.leaves[(size_t)of.cols.tweak], rows, key, 64);
+  t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
   decode_list_column(of.map, rg.cols[(size_t)of.cols.outputs], of.meta.leaves[(size_t)of.cols.outputs], rows, outs);
-  decode_blob_column(of.map, rg.cols[(size_t)of.cols.txid], of.meta.leaves[(size_t)of.cols.txid], rows, txid, 32);
-  decode_int32_column(of.map, rg.cols[(size_t)of.cols.height], of.meta.leaves[(size_t)of.cols.height], rows, height);
-  // a row with a NULL txid or height is dropped before the GPU (src/cudasp_extension.cu:195-197): make its key NULL
-  if (txid.valid.nulls || height.valid.nulls)
-    for (int64_t r = 0; r < rows; r++)
-      if (!txid.valid.get(r) || !height.valid.get(r)) key.valid.clear(r);
+  t1 = now_ns(); g_clock.ns[1] += t1 - t0; t0 = t1;
+  // txid and height are decoded AFTER the row group has been through the GPU: the scan does not need them, so the GPUs get their
+  // first rows a third sooner, and a row with a NULL txid or height -- which the reference drops before the GPU
+  // (src/cudasp_extension.cu:195-197) -- is dropped from the matches instead: the same result set.
 
   ArrowSchema ts{}, os{}, cs{};
   ArrowSchema *os_children[1] = {&cs};
@@ -895,19 +1012,27 @@ int scan_row_group(cudasp_query *q, const OpenFile &of, uint32_t file_index, siz
   os.format = "+l"; os.name = "outputs"; os.flags = ARROW_FLAG_NULLABLE; os.n_children = 1; os.children = os_children;
   ArrowArray ta{}, oa{}, ca{};
   ArrowArray *oa_children[1] = {&ca};
-  const void *tb[3] = {key.valid.nulls ? key.valid.bits.data() : nullptr, key.offsets.data(), key.data.empty() ? (const void *)"" : key.data.data()};
+  const void *tb[3] = {key.valid.nulls ? key.valid.bits.data() : nullptr, key.offsets.data(), key.data.empty() ? (const void *)"" : (const void *)key.data.data()};
   ta.length = rows; ta.null_count = key.valid.nulls; ta.n_buffers = 3; ta.buffers = tb;
-  const void *cb[2] = {outs.child_valid.nulls ? outs.child_valid.bits.data() : nullptr, outs.values.empty() ? (const void *)"" : (const void *)outs.values.data()};
-  ca.length = (int64_t)outs.values.size(); ca.null_count = outs.child_valid.nulls; ca.n_buffers = 2; ca.buffers = cb;
+  const void *cb[2] = {outs.child_valid.nulls ? outs.child_valid.bits.data() : nullptr, outs.n_values() ? (const void *)outs.values() : (const void *)""};
+  ca.length = (int64_t)outs.n_values(); ca.null_count = outs.child_valid.nulls; ca.n_buffers = 2; ca.buffers = cb;
   const void *ob[2] = {outs.valid.nulls ? outs.valid.bits.data() : nullptr, outs.offsets.data()};
   oa.length = rows; oa.null_count = outs.valid.nulls; oa.n_buffers = 2; oa.buffers = ob; oa.n_children = 1; oa.children = oa_children;
 
-  std::vector<uint64_t> ids((size_t)rows);
+  std::vector<uint64_t> &ids = sc.ids;
+  if (ids.size() < (size_t)rows) ids.resize((size_t)rows);
   uint64_t n = 0;
   const int rc = cudasp_scan_arrow_columns(q, &ts, &ta, &os, &oa, ids.data(), (uint64_t)rows, &n);
+  t1 = now_ns(); g_clock.ns[4] += t1 - t0; t0 = t1;
   if (rc) return rc;
+  if (n == 0) return 0;                       // nothing matched in this row group (the usual case): its txids are never looked at
+  decode_blob_column(of.map, rg.cols[(size_t)of.cols.txid], of.meta.leaves[(size_t)of.cols.txid], rows, txid, 32);
+  t1 = now_ns(); g_clock.ns[2] += t1 - t0; t0 = t1;
+  decode_int32_column(of.map, rg.cols[(size_t)of.cols.height], of.meta.leaves[(size_t)of.cols.height], rows, height);
+  t1 = now_ns(); g_clock.ns[3] += t1 - t0; t0 = t1;
   for (uint64_t k = 0; k < n; k++) {
     const size_t r = (size_t)ids[k];
+    if (!txid.valid.get((int64_t)r) || !height.valid.get((int64_t)r)) continue;
     Match m;
     m.file = file_index;
     m.row = (uint64_t)of.row_base[g] + r;
@@ -942,6 +1067,7 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
       OpenFile &of = files[(size_t)i];
       of.meta = read_footer(of.map);
       of.cols = map_columns(of.meta);
+      validate_columns(of.meta, of.cols);
       int64_t base = 0;
       for (size_t g = 0; g < of.meta.row_groups.size(); g++) {
         of.row_base.push_back(base);
@@ -963,13 +1089,14 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
   std::mutex err_mu;
   std::string err_msg;
   auto work = [&](int t) {
+    Scratch scratch;
     for (;;) {
       const size_t i = next.fetch_add(1);
       if (i >= items.size() || first_rc.load()) return;
       int rc = 0;
       std::string msg;
       try {
-        rc = scan_row_group(q, files[items[i].file], items[i].file, items[i].group, found[(size_t)t]);
+        rc = scan_row_group(q, files[items[i].file], items[i].file, items[i].group, found[(size_t)t], scratch);
         if (rc) msg = cudasp_last_error(q);
       } catch (const Unsupported &u) {
         rc = CUDASP_ERR_UNSUPPORTED; msg = "Parquet feature outside the fast path: " + u.what;
@@ -993,6 +1120,11 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
     for (int t = 1; t < threads; t++) th.emplace_back(work, t);
     work(0);
     for (auto &x : th) x.join();
+  }
+  if (getenv("CUDASP_TRACE")) {
+    fprintf(stderr, "[cudasp] scan_parquet: %llu rows, %d threads; seconds summed over threads: tweak_key %.3f, outputs %.3f, txid %.3f, height %.3f, "
+                    "staging + GPU %.3f\n", (unsigned long long)total_rows, threads, 1e-9 * g_clock.ns[0].exchange(0), 1e-9 * g_clock.ns[1].exchange(0),
+            1e-9 * g_clock.ns[2].exchange(0), 1e-9 * g_clock.ns[3].exchange(0), 1e-9 * g_clock.ns[4].exchange(0));
   }
   if (first_rc.load()) return stg::fail(q, first_rc.load(), err_msg.c_str());
   std::vector<Match> all;
