@@ -116,12 +116,20 @@ int format_of(int64_t key_size) {
 
 // Streams rows of any number of (key, list) column pairs through the query's staging slots; ids come back as global
 // row numbers (row_base + index in the pair), ascending per pair, pairs in push order.
+//
+// Pieces are cut across pushes: the rows a push leaves over stay in an OPEN piece (an acquired slot that is still being
+// filled) and the next push goes on filling it, so a stream of small record batches, or of Parquet row groups, reaches the
+// GPU in whole pieces (whole waves of the ladder kernel) instead of one under-filled launch per batch.  drain() submits
+// what is left.  A piece therefore holds one or more SEGMENTS, each a run of staged rows that came from one push.
 class ArrowScanner {
  public:
-  explicit ArrowScanner(cudasp_query *q) : q_(q), piece_(stg::piece_rows(q)) {
-    cur_ = std::min(piece_, std::max<uint32_t>(piece_ / 8, 8192u));     // ramp-up: see piece_now()
+  // ramp == false: full pieces from the start (the Parquet front-end runs one scanner per decoder thread and ramps only as
+  // many as there are devices)
+  explicit ArrowScanner(cudasp_query *q, bool ramp = true) : q_(q), piece_(stg::piece_rows(q)) {
+    cur_ = ramp ? std::min(piece_, std::max<uint32_t>(piece_ / 8, 8192u)) : piece_;     // ramp-up: see piece_now()
   }
   ~ArrowScanner() {
+    if (has_open_) stg::release(q_, &open_.s);       // never submitted
     for (Pending &p : pending_) {        // error exit: let the slot's stream finish before its staging is reused
       uint32_t n = 0;
       stg::finish(q_, &p.s, &n);
@@ -146,7 +154,7 @@ class ArrowScanner {
   }
 
   int drain() {
-    int rc = 0;
+    int rc = flush_open();
     while (!pending_.empty()) {
       int r = collect_front();
       if (!rc) rc = r;
@@ -155,16 +163,28 @@ class ArrowScanner {
   }
 
  private:
+  static constexpr uint32_t NO_MAP = 0xFFFFFFFFu;
+  struct Segment {
+    uint32_t staged_first;            // first staged row of the segment
+    uint32_t map_first;               // NO_MAP: staged row r is source row base + (r - staged_first); else rowmap[map_first + ...]
+    uint64_t base;                    // global row number the segment counts from
+  };
   struct Pending {
     Staging s;
-    uint64_t base;                    // global row number of the piece's first source row
-    std::vector<uint32_t> rowmap;     // general path: staged row -> source row - base; empty = identity
+    std::vector<Segment> segs;
+    std::vector<uint32_t> rowmap;     // general path: source row - base of its segment, one per staged row of mapped segments
   };
 
   cudasp_query *q_;
   uint32_t piece_;
   uint32_t cur_ = 0;
   std::deque<Pending> pending_;
+  // the piece being filled
+  Pending open_;
+  bool has_open_ = false;
+  uint32_t open_rows_ = 0, open_target_ = 0;
+  uint64_t open_nout_ = 0;
+  int open_fmt_ = -1;
 
   // rows for the next piece: the first pieces of a scan ramp up (1/8, 1/4, 1/2 of a full piece) so that the GPU starts
   // after a short host copy instead of idling through a full one
@@ -181,9 +201,13 @@ class ArrowScanner {
     uint32_t n = 0;
     int rc = stg::finish(q_, &p.s, &n);
     if (!rc) {
+      size_t g = 0;                   // ids ascend: the segment cursor only moves forward
       for (uint32_t i = 0; i < n; i++) {
         const uint32_t id = p.s.ids[i];
-        matches.push_back(p.base + (p.rowmap.empty() ? id : p.rowmap[id]));
+        while (g + 1 < p.segs.size() && p.segs[g + 1].staged_first <= id) g++;
+        const Segment &sg = p.segs[g];
+        const uint32_t r = id - sg.staged_first;
+        matches.push_back(sg.base + (sg.map_first == NO_MAP ? r : p.rowmap[sg.map_first + r]));
       }
     }
     stg::release(q_, &p.s);
@@ -204,58 +228,105 @@ class ArrowScanner {
     }
   }
 
-  // returns 0 = staged a piece (*a advanced), 1 = this piece needs the general path, < 0 = error
+  // makes sure there is an open piece of key format fmt (submits an open piece of the other format first)
+  int open_piece(int fmt) {
+    if (has_open_ && open_fmt_ != fmt) {
+      int rc = flush_open();
+      if (rc) return rc;
+    }
+    if (has_open_) return 0;
+    open_ = Pending{};
+    int rc = acquire(&open_.s);
+    if (rc) return rc;
+    has_open_ = true;
+    open_rows_ = 0;
+    open_nout_ = 0;
+    open_fmt_ = fmt;
+    open_target_ = std::min<uint32_t>(piece_now(), open_.s.cap_rows);
+    open_.s.offsets[0] = 0;
+    return 0;
+  }
+
+  // submits the open piece as it is (a full piece, a change of key format, no room for a row's outputs, or the end)
+  int flush_open() {
+    if (!has_open_) return 0;
+    has_open_ = false;
+    if (open_rows_ == 0) {
+      stg::release(q_, &open_.s);
+      return 0;
+    }
+    int rc = stg::submit(q_, &open_.s, open_rows_, open_nout_, open_fmt_);
+    if (rc) {
+      stg::release(q_, &open_.s);
+      return rc;
+    }
+    pending_.push_back(std::move(open_));
+    piece_done();
+    return 0;
+  }
+
+  // room for n more outputs in the open piece: 0 = yes, 1 = the piece was submitted to make room (open a new one), < 0 = error
+  int room_for_outputs(uint64_t n) {
+    if (open_nout_ + n <= open_.s.cap_outputs && open_nout_ + n <= 0xFFFFFFFFull) return 0;
+    if (open_rows_) {
+      int rc = flush_open();
+      return rc ? rc : 1;
+    }
+    if (n > 0xFFFFFFFFull) return stg::fail(q_, CUDASP_ERR_ARG, "outputs: more than 2^32 values in one piece");
+    return stg::reserve_outputs(q_, &open_.s, n);     // an empty piece: its staging may be replaced
+  }
+
+  // returns 0 = staged rows (*a advanced), 1 = these rows need the general path, < 0 = error
   int stage_dense(const KeyColumn &k, const ListColumn &l, uint64_t row_base, int64_t *a) {
     const int64_t base = *a;
     const int64_t w = k.size(base);
     const int fmt = format_of(w);
     if (fmt < 0) return 1;
-    const int64_t cnt = std::min<int64_t>(piece_now(), k.length - base);
-    if (!k.width) {                   // binary column: the piece must be one uniform width
-      bool uniform = true;
-      if (k.large) {
-        const int64_t *o = static_cast<const int64_t *>(k.offsets) + k.offset + base;
-        for (int64_t i = 0; i < cnt; i++) uniform &= (o[i + 1] - o[i]) == w;
-      } else {
-        const int32_t *o = static_cast<const int32_t *>(k.offsets) + k.offset + base;
-        for (int64_t i = 0; i < cnt; i++) uniform &= (o[i + 1] - o[i]) == w;
+    for (;;) {
+      int rc = open_piece(fmt);
+      if (rc) return rc;
+      const int64_t cnt = std::min<int64_t>(open_target_ - open_rows_, k.length - base);
+      if (!k.width) {                   // binary column: the rows must be one uniform width
+        bool uniform = true;
+        if (k.large) {
+          const int64_t *o = static_cast<const int64_t *>(k.offsets) + k.offset + base;
+          for (int64_t i = 0; i < cnt; i++) uniform &= (o[i + 1] - o[i]) == w;
+        } else {
+          const int32_t *o = static_cast<const int32_t *>(k.offsets) + k.offset + base;
+          for (int64_t i = 0; i < cnt; i++) uniform &= (o[i + 1] - o[i]) == w;
+        }
+        if (!uniform) return 1;
       }
-      if (!uniform) return 1;
+      const int64_t o0 = l.begin(base), o1 = l.begin(base + cnt);
+      const uint64_t no = (uint64_t)(o1 - o0);
+      if (o1 < o0 || no > 0xFFFFFFFFull) return stg::fail(q_, CUDASP_ERR_ARG, "outputs: offsets out of range");
+      rc = room_for_outputs(no);
+      if (rc < 0) return rc;
+      if (rc == 1) continue;            // a fresh piece has other room: cut again
+      Staging &s = open_.s;
+      memcpy(s.tweaks + (size_t)open_rows_ * w, k.data + k.begin(base), (size_t)cnt * w);
+      // rebase; a malformed batch (offsets going backwards) is refused here: the kernels index outputs[] with these
+      const uint32_t first = (uint32_t)open_nout_;
+      uint32_t prev = first, bad = 0;
+      uint32_t *so = s.offsets + open_rows_;
+      if (l.large) {
+        const int64_t *o = static_cast<const int64_t *>(l.offsets) + l.offset + base;
+        for (int64_t i = 0; i <= cnt; i++) { const uint32_t v = first + (uint32_t)(o[i] - o0); bad |= (uint32_t)(v < prev); so[i] = prev = v; }
+      } else {
+        const int32_t *o = static_cast<const int32_t *>(l.offsets) + l.offset + base;
+        for (int64_t i = 0; i <= cnt; i++) { const uint32_t v = first + (uint32_t)(o[i] - (int32_t)o0); bad |= (uint32_t)(v < prev); so[i] = prev = v; }
+      }
+      if (bad || prev != first + (uint32_t)no) {
+        so[0] = first;                  // the piece stays as it was before these rows
+        return stg::fail(q_, CUDASP_ERR_ARG, "outputs: list offsets are not monotonically non-decreasing");
+      }
+      if (no) memcpy(s.outputs + open_nout_, l.values + l.child_offset + o0, no * 8);
+      open_.segs.push_back(Segment{open_rows_, NO_MAP, row_base + (uint64_t)base});
+      open_rows_ += (uint32_t)cnt;
+      open_nout_ += no;
+      *a = base + cnt;
+      return open_rows_ == open_target_ ? flush_open() : 0;
     }
-    const int64_t o0 = l.begin(base), o1 = l.begin(base + cnt);
-    const uint64_t no = (uint64_t)(o1 - o0);
-    if (o1 < o0 || no > 0xFFFFFFFFull) return stg::fail(q_, CUDASP_ERR_ARG, "outputs: offsets out of range");
-    Staging s;
-    int rc = acquire(&s);
-    if (rc) return rc;
-    if (no > s.cap_outputs && (rc = stg::reserve_outputs(q_, &s, no))) {
-      stg::release(q_, &s);
-      return rc;
-    }
-    memcpy(s.tweaks, k.data + k.begin(base), (size_t)cnt * w);
-    // rebase; a malformed batch (offsets going backwards) is refused here: the kernels index outputs[] with these
-    uint32_t prev = 0, bad = 0;
-    if (l.large) {
-      const int64_t *o = static_cast<const int64_t *>(l.offsets) + l.offset + base;
-      for (int64_t i = 0; i <= cnt; i++) { const uint32_t v = (uint32_t)(o[i] - o0); bad |= (uint32_t)(v < prev); s.offsets[i] = prev = v; }
-    } else {
-      const int32_t *o = static_cast<const int32_t *>(l.offsets) + l.offset + base;
-      for (int64_t i = 0; i <= cnt; i++) { const uint32_t v = (uint32_t)(o[i] - (int32_t)o0); bad |= (uint32_t)(v < prev); s.offsets[i] = prev = v; }
-    }
-    if (bad || prev != (uint32_t)no) {
-      stg::release(q_, &s);
-      return stg::fail(q_, CUDASP_ERR_ARG, "outputs: list offsets are not monotonically non-decreasing");
-    }
-    if (no) memcpy(s.outputs, l.values + l.child_offset + o0, no * 8);
-    rc = stg::submit(q_, &s, (uint32_t)cnt, no, fmt);
-    if (rc) {
-      stg::release(q_, &s);
-      return rc;
-    }
-    pending_.push_back(Pending{s, row_base + (uint64_t)base, {}});
-    piece_done();
-    *a = base + cnt;
-    return 0;
   }
 
   int stage_general(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity, int64_t rv_off, uint64_t row_base,
@@ -279,59 +350,40 @@ int ArrowScanner::stage_general(const KeyColumn &k, const ListColumn &l, const u
   }
   const int64_t first = i;
   const int64_t w = k.size(first);
-  const int fmt = format_of(w);
-  Staging s;
-  int rc = acquire(&s);
+  int rc = open_piece(format_of(w));
   if (rc) return rc;
-  Pending p{s, row_base + (uint64_t)first, {}};
-  const uint32_t cap = std::min<uint32_t>(piece_now(), p.s.cap_rows);
-  p.rowmap.reserve(cap);
-  uint32_t rows = 0;
-  uint64_t n_out = 0;
-  p.s.offsets[0] = 0;
-  for (; i < n && rows < cap; i++) {
+  open_.segs.push_back(Segment{open_rows_, (uint32_t)open_.rowmap.size(), row_base + (uint64_t)first});
+  const uint32_t seg_first = open_rows_;
+  for (; i < n && open_rows_ < open_target_; i++) {
     if (dropped(i)) continue;
     if (k.size(i) != w) break;                       // the other key format: next piece
     int64_t b = 0, e = 0;
     if (l.valid(i)) {
       b = l.begin(i);
       e = l.begin(i + 1);
-      if (e < b) {
-        stg::release(q_, &p.s);
-        return stg::fail(q_, CUDASP_ERR_ARG, "outputs: offsets not monotonic");
-      }
+      if (e < b) return stg::fail(q_, CUDASP_ERR_ARG, "outputs: offsets not monotonic");
     }
     const uint64_t len = (uint64_t)(e - b);
-    if (n_out + len > p.s.cap_outputs) {
-      if (rows) break;                               // cut the piece here
-      if ((rc = stg::reserve_outputs(q_, &p.s, len))) {
-        stg::release(q_, &p.s);
-        return rc;
-      }
+    if (open_nout_ + len > open_.s.cap_outputs || open_nout_ + len > 0xFFFFFFFFull) {
+      if (open_rows_) break;                         // cut the piece here
+      if ((rc = room_for_outputs(len)) < 0) return rc;
     }
-    memcpy(p.s.tweaks + (size_t)rows * w, k.data + k.begin(i), (size_t)w);
+    Staging &s = open_.s;
+    memcpy(s.tweaks + (size_t)open_rows_ * w, k.data + k.begin(i), (size_t)w);
     if (l.child_validity) {
       for (int64_t j = b; j < e; j++)
-        if (l.child_valid(j)) p.s.outputs[n_out++] = l.values[l.child_offset + j];
+        if (l.child_valid(j)) s.outputs[open_nout_++] = l.values[l.child_offset + j];
     } else if (len) {
-      memcpy(p.s.outputs + n_out, l.values + l.child_offset + b, len * 8);
-      n_out += len;
+      memcpy(s.outputs + open_nout_, l.values + l.child_offset + b, len * 8);
+      open_nout_ += len;
     }
-    if (n_out > 0xFFFFFFFFull) {
-      stg::release(q_, &p.s);
-      return stg::fail(q_, CUDASP_ERR_ARG, "outputs: more than 2^32 values in one piece");
-    }
-    p.rowmap.push_back((uint32_t)(i - first));
-    p.s.offsets[++rows] = (uint32_t)n_out;
+    open_.rowmap.push_back((uint32_t)(i - first));
+    s.offsets[++open_rows_] = (uint32_t)open_nout_;
   }
   *a = i;
-  rc = stg::submit(q_, &p.s, rows, n_out, fmt);
-  if (rc) {
-    stg::release(q_, &p.s);
-    return rc;
-  }
-  pending_.push_back(std::move(p));
-  piece_done();
+  if (open_rows_ == seg_first) open_.segs.pop_back();          // nothing staged (no room): the piece is cut below
+  // submit when full, or when it was cut short (no room for the next row's outputs, or the other key format follows)
+  if (open_rows_ == open_target_ || i < n) return flush_open();
   return 0;
 }
 
@@ -372,7 +424,38 @@ int parse_batch(cudasp_query *q, const ArrowSchema *schema, const ArrowArray *ba
   return 0;
 }
 
+
+int parse_pair(cudasp_query *q, const ArrowSchema *tweak_schema, const ArrowArray *tweak_key, const ArrowSchema *outputs_schema,
+               const ArrowArray *outputs, KeyColumn *k, ListColumn *l) {
+  int rc = parse_key_column(q, tweak_schema, tweak_key, k);
+  if (rc) return rc;
+  if ((rc = parse_list_column(q, outputs_schema, outputs, l))) return rc;
+  if (k->length != l->length) return stg::fail(q, CUDASP_ERR_ARG, "tweak_key and outputs differ in length");
+  return 0;
+}
+
 }  // namespace
+
+struct csp::staging::ColumnScan {
+  cudasp_query *q;
+  ArrowScanner sc;
+  ColumnScan(cudasp_query *query, bool ramp) : q(query), sc(query, ramp) {}
+};
+csp::staging::ColumnScan *csp::staging::column_scan_open(cudasp_query *q, bool ramp) { return new ColumnScan(q, ramp); }
+int csp::staging::column_scan_push(ColumnScan *cs, const ArrowSchema *tweak_schema, const ArrowArray *tweak_key,
+                                   const ArrowSchema *outputs_schema, const ArrowArray *outputs, uint64_t row_base) {
+  KeyColumn k;
+  ListColumn l;
+  int rc = parse_pair(cs->q, tweak_schema, tweak_key, outputs_schema, outputs, &k, &l);
+  return rc ? rc : cs->sc.push(k, l, nullptr, 0, row_base);
+}
+int csp::staging::column_scan_finish(ColumnScan *cs, const uint64_t **rows, uint64_t *n) {
+  int rc = cs->sc.drain();
+  *rows = cs->sc.matches.data();
+  *n = cs->sc.matches.size();
+  return rc;
+}
+void csp::staging::column_scan_close(ColumnScan *cs) { delete cs; }
 
 extern "C" {
 
@@ -383,10 +466,8 @@ int cudasp_scan_arrow_columns(cudasp_query *q, const ArrowSchema *tweak_schema, 
   *n_matches = 0;
   KeyColumn k;
   ListColumn l;
-  int rc = parse_key_column(q, tweak_schema, tweak_key, &k);
+  int rc = parse_pair(q, tweak_schema, tweak_key, outputs_schema, outputs, &k, &l);
   if (rc) return rc;
-  if ((rc = parse_list_column(q, outputs_schema, outputs, &l))) return rc;
-  if (k.length != l.length) return stg::fail(q, CUDASP_ERR_ARG, "tweak_key and outputs differ in length");
   ArrowScanner sc(q);
   if ((rc = sc.push(k, l, nullptr, 0, 0))) return rc;
   if ((rc = sc.drain())) return rc;

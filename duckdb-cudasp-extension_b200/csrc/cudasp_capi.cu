@@ -827,6 +827,7 @@ void release(cudasp_query *q, Staging *v) {
   v->slot = nullptr;
 }
 uint32_t piece_rows(cudasp_query *q) { return std::min<uint32_t>(q->batch_rows, q->piece_rows); }
+int device_count(cudasp_query *q) { return (int)q->devs.size(); }
 int fail(cudasp_query *q, int code, const char *msg) { return ::fail(q, code, msg); }
 }  // namespace staging
 }  // namespace csp

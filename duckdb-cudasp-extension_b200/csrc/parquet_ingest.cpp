@@ -988,22 +988,21 @@ struct Scratch {               // one per decoder thread: the decoded columns of
   ListColumn outs;
   std::vector<uint64_t> ids;
 };
-int scan_row_group(cudasp_query *q, const OpenFile &of, uint32_t file_index, size_t g, std::vector<Match> &matches, Scratch &sc) {
+// Decodes tweak_key and outputs of one row group and stages its rows into the thread's scan; their row numbers count from
+// row_base.  txid and height are NOT decoded here: the scan does not need them, so the GPUs get their first rows a third
+// sooner; collect_matches() decodes them for the (few) row groups that held a match.
+int push_row_group(stg::ColumnScan *scan, const OpenFile &of, size_t g, uint64_t row_base, Scratch &sc) {
   const RowGroupMeta &rg = of.meta.row_groups[g];
   const int64_t rows = rg.num_rows;
   if (rows == 0) return 0;
   if (rows > 0x7fffffff) unsupported("more than 2^31 rows in one row group");
-  BlobColumn &txid = sc.txid, &key = sc.key;
-  Int32Column &height = sc.height;
+  BlobColumn &key = sc.key;
   ListColumn &outs = sc.outs;
   uint64_t t0 = now_ns(), t1;
   decode_blob_column(of.map, rg.cols[(size_t)of.cols.tweak], of.meta.leaves[(size_t)of.cols.tweak], rows, key, 64);
   t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
   decode_list_column(of.map, rg.cols[(size_t)of.cols.outputs], of.meta.leaves[(size_t)of.cols.outputs], rows, outs);
   t1 = now_ns(); g_clock.ns[1] += t1 - t0; t0 = t1;
-  // txid and height are decoded AFTER the row group has been through the GPU: the scan does not need them, so the GPUs get their
-  // first rows a third sooner, and a row with a NULL txid or height -- which the reference drops before the GPU
-  // (src/cudasp_extension.cu:195-197) -- is dropped from the matches instead: the same result set.
 
   ArrowSchema ts{}, os{}, cs{};
   ArrowSchema *os_children[1] = {&cs};
@@ -1018,20 +1017,28 @@ int scan_row_group(cudasp_query *q, const OpenFile &of, uint32_t file_index, siz
   ca.length = (int64_t)outs.n_values(); ca.null_count = outs.child_valid.nulls; ca.n_buffers = 2; ca.buffers = cb;
   const void *ob[2] = {outs.valid.nulls ? outs.valid.bits.data() : nullptr, outs.offsets.data()};
   oa.length = rows; oa.null_count = outs.valid.nulls; oa.n_buffers = 2; oa.buffers = ob; oa.n_children = 1; oa.children = oa_children;
+  const int rc = stg::column_scan_push(scan, &ts, &ta, &os, &oa, row_base);
+  t1 = now_ns(); g_clock.ns[4] += t1 - t0;
+  return rc;
+}
 
-  std::vector<uint64_t> &ids = sc.ids;
-  if (ids.size() < (size_t)rows) ids.resize((size_t)rows);
-  uint64_t n = 0;
-  const int rc = cudasp_scan_arrow_columns(q, &ts, &ta, &os, &oa, ids.data(), (uint64_t)rows, &n);
-  t1 = now_ns(); g_clock.ns[4] += t1 - t0; t0 = t1;
-  if (rc) return rc;
-  if (n == 0) return 0;                       // nothing matched in this row group (the usual case): its txids are never looked at
+// The matching rows ids[0..n) of one row group (ascending) -> Match records.  A row with a NULL txid or height, which the
+// reference drops before the GPU (src/cudasp_extension.cu:195-197), is dropped here instead: the same result set.
+void collect_matches(const OpenFile &of, uint32_t file_index, size_t g, const uint32_t *ids, size_t n, std::vector<Match> &matches, Scratch &sc) {
+  const RowGroupMeta &rg = of.meta.row_groups[g];
+  const int64_t rows = rg.num_rows;
+  BlobColumn &txid = sc.txid, &key = sc.key;
+  Int32Column &height = sc.height;
+  uint64_t t0 = now_ns(), t1;
+  decode_blob_column(of.map, rg.cols[(size_t)of.cols.tweak], of.meta.leaves[(size_t)of.cols.tweak], rows, key, 64);
+  t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
   decode_blob_column(of.map, rg.cols[(size_t)of.cols.txid], of.meta.leaves[(size_t)of.cols.txid], rows, txid, 32);
   t1 = now_ns(); g_clock.ns[2] += t1 - t0; t0 = t1;
   decode_int32_column(of.map, rg.cols[(size_t)of.cols.height], of.meta.leaves[(size_t)of.cols.height], rows, height);
-  t1 = now_ns(); g_clock.ns[3] += t1 - t0; t0 = t1;
-  for (uint64_t k = 0; k < n; k++) {
-    const size_t r = (size_t)ids[k];
+  t1 = now_ns(); g_clock.ns[3] += t1 - t0;
+  for (size_t k = 0; k < n; k++) {
+    const size_t r = ids[k];
+    if ((int64_t)r >= rows) corrupt("a match outside its row group");
     if (!txid.valid.get((int64_t)r) || !height.valid.get((int64_t)r)) continue;
     Match m;
     m.file = file_index;
@@ -1041,7 +1048,6 @@ int scan_row_group(cudasp_query *q, const OpenFile &of, uint32_t file_index, siz
     m.key.assign(reinterpret_cast<const char *>(key.data.data()) + key.offsets[r], (size_t)(key.offsets[r + 1] - key.offsets[r]));
     matches.push_back(std::move(m));
   }
-  return 0;
 }
 
 struct ResultOwner : cudasp_parquet_result {           // the public struct and the buffers it points into
@@ -1088,29 +1094,54 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
   std::atomic<int> first_rc{0};
   std::mutex err_mu;
   std::string err_msg;
+  // One scan per thread, spanning the row groups the thread takes: their rows fill the same pieces (csrc/arrow_ingest.cpp), so
+  // the GPUs see whole pieces whatever the row-group size.  A row's number inside the scan is (item << 32) | row in the group.
+  // Only as many threads as there are devices start with ramped-up (small) pieces -- enough for every GPU to start early.
+  const int n_devices = stg::device_count(q);
   auto work = [&](int t) {
     Scratch scratch;
-    for (;;) {
-      const size_t i = next.fetch_add(1);
-      if (i >= items.size() || first_rc.load()) return;
-      int rc = 0;
-      std::string msg;
-      try {
-        rc = scan_row_group(q, files[items[i].file], items[i].file, items[i].group, found[(size_t)t], scratch);
-        if (rc) msg = cudasp_last_error(q);
-      } catch (const Unsupported &u) {
-        rc = CUDASP_ERR_UNSUPPORTED; msg = "Parquet feature outside the fast path: " + u.what;
-      } catch (const Corrupt &c) {
-        rc = CUDASP_ERR_IO; msg = "malformed Parquet file: " + c.what;
-      } catch (const std::bad_alloc &) {
-        rc = CUDASP_ERR_IO; msg = "out of host memory while decoding a row group";
+    stg::ColumnScan *scan = nullptr;
+    int rc = 0;
+    std::string msg;
+    try {
+      scan = stg::column_scan_open(q, t < n_devices);
+      for (;;) {
+        const size_t i = next.fetch_add(1);
+        if (i >= items.size() || first_rc.load()) break;
+        rc = push_row_group(scan, files[items[i].file], items[i].group, (uint64_t)i << 32, scratch);
+        if (rc) break;
       }
+      const uint64_t *ids = nullptr;
+      uint64_t n = 0;
+      const uint64_t t0 = now_ns();
+      const int rc2 = stg::column_scan_finish(scan, &ids, &n);       // also after an error: lets the pieces in flight finish
+      g_clock.ns[4] += now_ns() - t0;
       if (rc) {
-        std::lock_guard<std::mutex> lk(err_mu);
-        int expected = 0;
-        if (first_rc.compare_exchange_strong(expected, rc)) err_msg = msg;
-        return;
+        msg = cudasp_last_error(q);
+      } else if (rc2) {
+        rc = rc2;
+        msg = cudasp_last_error(q);
       }
+      std::vector<uint32_t> in_group;
+      for (uint64_t a = 0; !rc && !first_rc.load() && a < n;) {      // ids: grouped by item in push order, ascending inside
+        const size_t i = (size_t)(ids[a] >> 32);
+        if (i >= items.size()) corrupt("a match outside the files");
+        in_group.clear();
+        for (; a < n && (size_t)(ids[a] >> 32) == i; a++) in_group.push_back((uint32_t)ids[a]);
+        collect_matches(files[items[i].file], items[i].file, items[i].group, in_group.data(), in_group.size(), found[(size_t)t], scratch);
+      }
+    } catch (const Unsupported &u) {
+      rc = CUDASP_ERR_UNSUPPORTED; msg = "Parquet feature outside the fast path: " + u.what;
+    } catch (const Corrupt &c) {
+      rc = CUDASP_ERR_IO; msg = "malformed Parquet file: " + c.what;
+    } catch (const std::bad_alloc &) {
+      rc = CUDASP_ERR_IO; msg = "out of host memory while decoding a row group";
+    }
+    if (scan) stg::column_scan_close(scan);         // waits for pieces still in flight
+    if (rc) {
+      std::lock_guard<std::mutex> lk(err_mu);
+      int expected = 0;
+      if (first_rc.compare_exchange_strong(expected, rc)) err_msg = msg;
     }
   };
   if (threads == 1) {

@@ -6,6 +6,8 @@
 #include <cstdint>
 
 struct cudasp_query;
+struct ArrowSchema;
+struct ArrowArray;
 
 namespace csp {
 namespace staging {
@@ -33,7 +35,23 @@ CSP_HIDDEN int finish(cudasp_query *q, Staging *s, uint32_t *n);
 CSP_HIDDEN void release(cudasp_query *q, Staging *s);
 // rows per piece a synchronous call should stream in (whole K1 waves, <= batch_rows)
 CSP_HIDDEN uint32_t piece_rows(cudasp_query *q);
+// devices the query spreads its slots over
+CSP_HIDDEN int device_count(cudasp_query *q);
 CSP_HIDDEN int fail(cudasp_query *q, int code, const char *msg);
+
+
+// A scan that spans several (tweak_key, outputs) array pairs, for front-ends that produce them one after another on one thread
+// (parquet_ingest.cpp: one pair per row group).  arrow_ingest.cpp: rows of consecutive pushes fill the same pieces, so the GPU
+// sees whole pieces whatever the size of the pairs.  Column types and NULL rules are cudasp_scan_arrow_columns'.
+struct ColumnScan;
+// ramp: start with small pieces (the first rows reach the GPU sooner); a front-end with many threads ramps only a few
+CSP_HIDDEN ColumnScan *column_scan_open(cudasp_query *q, bool ramp);
+// stages the pair's rows (copied: the arrays may be reused on return); their row numbers count from row_base
+CSP_HIDDEN int column_scan_push(ColumnScan *cs, const ArrowSchema *tweak_schema, const ArrowArray *tweak_key,
+                                const ArrowSchema *outputs_schema, const ArrowArray *outputs, uint64_t row_base);
+// submits what is left and waits; *rows (owned by the scan) = the matching row numbers, pairs in push order
+CSP_HIDDEN int column_scan_finish(ColumnScan *cs, const uint64_t **rows, uint64_t *n);
+CSP_HIDDEN void column_scan_close(ColumnScan *cs);
 
 }  // namespace staging
 }  // namespace csp

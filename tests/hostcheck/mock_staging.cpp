@@ -99,6 +99,7 @@ void release(cudasp_query *, Staging *v) {
   v->slot = nullptr;
 }
 uint32_t piece_rows(cudasp_query *q) { return q->piece; }
+int device_count(cudasp_query *) { return 1; }
 int fail(cudasp_query *q, int code, const char *msg) {
   static std::string last;
   last = msg;

@@ -216,3 +216,43 @@ def test_first_pieces_ramp_up(A):
     assert np.array_equal(ids, np.arange(0, n, 2, dtype=np.uint64))
     # 8192 + 16384 + 32768 + 65536 * 3 + 46040 = 300000 -> 7 pieces instead of ceil(300000 / 65536) = 5
     assert st["submits"] == 7 and st["rows"] == n
+
+
+def test_small_batches_fill_whole_pieces(A):
+    """Rows that a batch leaves over stay in an open piece which the next batch goes on filling: a stream of small record
+    batches reaches the device in whole pieces, and a piece made of several batches (dense ones and ones with NULLs, which go
+    row by row) still maps its matches back to global row numbers."""
+    parts, expect, base = [], [], 0
+    sizes = [100, 37, 1, 0, 250, 64, 90, 5, 333, 128, 19]
+    for s, n in enumerate(sizes):
+        keys, lists, e = make_rows(n, 40 + s, p_match=0.3, p_null_key=0.1 if s % 3 == 1 else 0.0,
+                                   p_null_child=0.2 if s % 3 == 2 else 0.0)
+        parts.append(batch_of(keys, lists))
+        expect.extend((e + base).tolist())
+        base += n
+    staged = sum(sum(k is not None for k in p.column("tweak_key").to_pylist()) for p in parts)
+    with A.query(piece=128, cap_rows=128, cap_outputs=4096, slots=3) as q:
+        reader = pa.RecordBatchReader.from_batches(parts[0].schema, parts)
+        ids, seen = A.arrow.scan_stream(q.h, reader, _lib=A.lib)
+        st = q.stats()
+    assert ids.tolist() == expect and seen == base
+    assert st["rows"] == staged
+    # whole pieces of 128 and one tail (a piece this small does not ramp) -- not one under-filled piece per batch
+    assert st["submits"] == -(-staged // 128) < len([n for n in sizes if n])
+
+
+def test_open_piece_is_cut_when_outputs_do_not_fit(A):
+    """An open piece with no room left for the next rows' outputs is submitted as it is; the rows start a new piece."""
+    n = 40
+    keys = [bytes([i]) * 64 for i in range(n)]
+    want = [int.from_bytes(k[1:9], "little", signed=True) for k in keys]
+    lists = [[want[i]] + [7] * 9 for i in range(n)]              # 10 outputs per row, every row matches
+    batches = [batch_of(keys[i:i + 8], lists[i:i + 8]) for i in range(0, n, 8)]
+    with A.query(piece=64, cap_rows=64, cap_outputs=128, slots=2) as q:
+        reader = pa.RecordBatchReader.from_batches(batches[0].schema, batches)
+        ids, seen = A.arrow.scan_stream(q.h, reader, _lib=A.lib)
+        st = q.stats()
+    assert ids.tolist() == list(range(n)) and seen == n
+    assert st["rows"] == n and st["outputs"] == 10 * n and st["reserves"] == 0
+    # 128 outputs hold 12 rows; the dense path does not split a batch of 8 to fill the last 4: 8 rows a piece
+    assert st["submits"] == 5

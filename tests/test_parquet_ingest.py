@@ -34,12 +34,13 @@ def P():
     L.mock_query_create.argtypes = [C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32]
     L.mock_query_destroy.argtypes = [C.c_void_p]
     L.mock_busy_slots.argtypes = [C.c_void_p]
+    L.mock_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     L.cudasp_last_error.restype = C.c_char_p
     L.cudasp_last_error.argtypes = [C.c_void_p]
     L.cudasp_scan_parquet.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int, C.c_int, C.POINTER(C.POINTER(Result))]
     L.cudasp_parquet_result_free.argtypes = [C.POINTER(Result)]
 
-    def scan(paths, piece=97, cap_rows=128, cap_outputs=1024):
+    def scan(paths, piece=97, cap_rows=128, cap_outputs=1024, stats=None):
         q = L.mock_query_create(piece, cap_rows, cap_outputs, 3)
         try:
             arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
@@ -55,6 +56,10 @@ def P():
             rows = r.rows_scanned
             L.cudasp_parquet_result_free(out)
             assert L.mock_busy_slots(q) == 0, "a staging slot leaked"
+            if stats is not None:
+                st = (C.c_uint64 * 6)()
+                L.mock_stats(q, st)
+                stats.update(submits=st[0], rows=st[1])
             return 0, (rows, got)
         finally:
             L.mock_query_destroy(q)
@@ -189,3 +194,18 @@ def test_files_written_by_duckdb(P, tmp_path, codec):
     rc, res = P([dst], piece=4000, cap_rows=4096, cap_outputs=40000)
     assert rc == 0, res
     assert res[0] == 40000 and [(g[1], g[2], g[3], g[4]) for g in res[1]] == expect
+
+
+def test_pieces_span_row_groups(P, tmp_path):
+    """Row groups smaller than a piece: the rows of consecutive row groups (and files) fill the same pieces, and a match is
+    still reported with its own file, row, txid, height and key."""
+    rows, expect = make_rows(2000, 77)
+    path = str(tmp_path / "small_groups.parquet")
+    pq.write_table(table_of(rows), path, row_group_size=50, compression="NONE")
+    assert pq.ParquetFile(path).metadata.num_row_groups == 40
+    st = {}
+    rc, res = P([path, path], piece=128, cap_rows=128, cap_outputs=4096, stats=st)
+    assert rc == 0, res
+    assert res[0] == 4000
+    assert [(g[0],) + g[1:] for g in res[1]] == [(0,) + e for e in expect] + [(1,) + e for e in expect]
+    assert st["rows"] == 4000 and st["submits"] == -(-4000 // 128)         # 32 pieces, not 80
