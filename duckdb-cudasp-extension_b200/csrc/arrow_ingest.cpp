@@ -449,6 +449,10 @@ int csp::staging::column_scan_push(ColumnScan *cs, const ArrowSchema *tweak_sche
   int rc = parse_pair(cs->q, tweak_schema, tweak_key, outputs_schema, outputs, &k, &l);
   return rc ? rc : cs->sc.push(k, l, nullptr, 0, row_base);
 }
+void csp::staging::column_scan_matches(ColumnScan *cs, const uint64_t **rows, uint64_t *n) {
+  *rows = cs->sc.matches.data();
+  *n = cs->sc.matches.size();
+}
 int csp::staging::column_scan_finish(ColumnScan *cs, const uint64_t **rows, uint64_t *n) {
   int rc = cs->sc.drain();
   *rows = cs->sc.matches.data();

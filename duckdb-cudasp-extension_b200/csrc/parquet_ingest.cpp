@@ -486,6 +486,7 @@ PageHeader read_page_header(Thrift &t) {
 // One data page, ready to decode: levels and values located, decompressed if need be.
 struct Page {
   int32_t num_values = 0, encoding = 0;
+  bool skipped = false;         // a page none of whose rows is wanted (ChunkReader::want): only num_values is set
   const uint8_t *rep = nullptr, *rep_end = nullptr, *def = nullptr, *def_end = nullptr, *values = nullptr, *values_end = nullptr;
   std::vector<uint8_t> buf;     // backing store when the page was compressed
 };
@@ -503,7 +504,14 @@ struct ChunkReader {
   const uint8_t *p, *end;
   int64_t values_left;
   Dictionary dict;
-  ChunkReader(const MappedFile &file, const ChunkMeta &c, const Leaf &l) : f(file), cm(c), leaf(l), values_left(c.num_values) {
+  // Row filter for FLAT columns (one value slot per row): when set, a data page that holds none of the wanted rows of the
+  // row group (ascending) comes back as `skipped` -- not decompressed, not decoded.  collect_matches() reads the few pages
+  // that hold a matching row this way instead of whole column chunks.
+  const uint32_t *want = nullptr;
+  size_t n_want = 0, want_pos = 0;
+  int64_t row_pos = 0;
+  ChunkReader(const MappedFile &file, const ChunkMeta &c, const Leaf &l, const uint32_t *wanted = nullptr, size_t n_wanted = 0)
+      : f(file), cm(c), leaf(l), values_left(c.num_values), want(wanted), n_want(n_wanted) {
     if (c.codec != C_UNCOMPRESSED && c.codec != C_SNAPPY) unsupported("compression codec " + std::to_string(c.codec) + " (only uncompressed and Snappy pages are decoded)");
     int64_t start = c.data_page_offset;
     if (c.dict_page_offset > 0 && c.dict_page_offset < start) start = c.dict_page_offset;
@@ -515,7 +523,7 @@ struct ChunkReader {
 #define MADV_POPULATE_READ 22
 #endif
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)4095;
-    madvise(reinterpret_cast<void *>(a0), (size_t)(reinterpret_cast<uintptr_t>(end) - a0), MADV_POPULATE_READ);
+    if (!want) madvise(reinterpret_cast<void *>(a0), (size_t)(reinterpret_cast<uintptr_t>(end) - a0), MADV_POPULATE_READ);
   }
   void load_dictionary(const PageHeader &h, const uint8_t *body) {
     if (h.encoding != E_PLAIN && h.encoding != E_PLAIN_DICT) unsupported("dictionary page encoding " + std::to_string(h.encoding));
@@ -555,6 +563,16 @@ struct ChunkReader {
       if (h.type != P_DATA && h.type != P_DATA_V2) unsupported("page type " + std::to_string(h.type));
       pg.num_values = h.num_values;
       pg.encoding = h.encoding;
+      pg.skipped = false;
+      if (want) {
+        while (want_pos < n_want && (int64_t)want[want_pos] < row_pos) want_pos++;
+        pg.skipped = want_pos == n_want || (int64_t)want[want_pos] >= row_pos + h.num_values;
+        row_pos += h.num_values;
+        if (pg.skipped) {
+          values_left -= h.num_values;
+          return true;
+        }
+      }
       pg.rep = pg.rep_end = pg.def = pg.def_end = nullptr;
       const uint8_t *b = body, *be = body + h.compressed;
       if (h.type == P_DATA) {
@@ -690,16 +708,20 @@ void page_blobs(const ChunkReader &cr, const Page &pg, int64_t n_present, Put pu
   }
 }
 
-void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf, int64_t rows, BlobColumn &out, size_t size_hint) {
+// want / n_want: only the pages that hold these rows (ascending) are decoded; every other row reads as an empty value
+void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf, int64_t rows, BlobColumn &out, size_t size_hint,
+                        const uint32_t *want = nullptr, size_t n_want = 0) {
   if (lf.type != T_BYTE_ARRAY && lf.type != T_FLBA) unsupported("column " + lf.path[0] + " is not BYTE_ARRAY / FIXED_LEN_BYTE_ARRAY");
   if (lf.max_rep != 0 || lf.max_def > 1) unsupported("column " + lf.path[0] + " is nested");
   if (lf.type == T_FLBA && cm.dict_page_offset > 0 && lf.type_length <= 0) corrupt("fixed-length column without a length");
-  ChunkReader cr(f, cm, lf);
+  ChunkReader cr(f, cm, lf, want, n_want);
   out.offsets.resize((size_t)rows + 1);
   out.offsets[0] = 0;
   out.data.clear();
-  out.data.grow((size_t)rows * size_hint);
-  out.data.clear();
+  if (!want) {
+    out.data.grow((size_t)rows * size_hint);
+    out.data.clear();
+  }
   out.valid.init(rows);
   int64_t row = 0;
   Page pg;
@@ -707,6 +729,12 @@ void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
   while (cr.next(pg)) {
     const int64_t n = pg.num_values;
     if (row + n > rows) corrupt("column " + lf.path[0] + ": more values than the row group has rows");
+    if (pg.skipped) {
+      const int32_t at = (int32_t)out.data.size();
+      for (int64_t k = 0; k < n; k++) out.offsets[(size_t)(row + k) + 1] = at;
+      row += n;
+      continue;
+    }
     int64_t present = n;
     bool all_valid = true;
     if (lf.max_def) {
@@ -750,10 +778,11 @@ void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
   if (row != rows) corrupt("column " + lf.path[0] + ": fewer values than the row group has rows");
 }
 
-void decode_int32_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf, int64_t rows, Int32Column &out) {
+void decode_int32_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf, int64_t rows, Int32Column &out,
+                         const uint32_t *want = nullptr, size_t n_want = 0) {
   if (lf.type != T_INT32) unsupported("column " + lf.path[0] + " is not INT32");
   if (lf.max_rep != 0 || lf.max_def > 1) unsupported("column " + lf.path[0] + " is nested");
-  ChunkReader cr(f, cm, lf);
+  ChunkReader cr(f, cm, lf, want, n_want);
   out.values.assign((size_t)rows, 0);
   out.valid.init(rows);
   int64_t row = 0;
@@ -762,6 +791,10 @@ void decode_int32_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &l
   while (cr.next(pg)) {
     const int64_t n = pg.num_values;
     if (row + n > rows) corrupt("column " + lf.path[0] + ": more values than rows");
+    if (pg.skipped) {
+      row += n;
+      continue;
+    }
     defs.assign((size_t)n, 1);
     if (lf.max_def) {
       HybridDecoder d;
@@ -1030,15 +1063,17 @@ void collect_matches(const OpenFile &of, uint32_t file_index, size_t g, const ui
   BlobColumn &txid = sc.txid, &key = sc.key;
   Int32Column &height = sc.height;
   uint64_t t0 = now_ns(), t1;
-  decode_blob_column(of.map, rg.cols[(size_t)of.cols.tweak], of.meta.leaves[(size_t)of.cols.tweak], rows, key, 64);
+  for (size_t k = 0; k < n; k++)
+    if ((int64_t)ids[k] >= rows || (k && ids[k] <= ids[k - 1])) corrupt("a match outside its row group");
+  // only the pages that hold a matching row are read (ChunkReader::want)
+  decode_blob_column(of.map, rg.cols[(size_t)of.cols.tweak], of.meta.leaves[(size_t)of.cols.tweak], rows, key, 64, ids, n);
   t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
-  decode_blob_column(of.map, rg.cols[(size_t)of.cols.txid], of.meta.leaves[(size_t)of.cols.txid], rows, txid, 32);
+  decode_blob_column(of.map, rg.cols[(size_t)of.cols.txid], of.meta.leaves[(size_t)of.cols.txid], rows, txid, 32, ids, n);
   t1 = now_ns(); g_clock.ns[2] += t1 - t0; t0 = t1;
-  decode_int32_column(of.map, rg.cols[(size_t)of.cols.height], of.meta.leaves[(size_t)of.cols.height], rows, height);
+  decode_int32_column(of.map, rg.cols[(size_t)of.cols.height], of.meta.leaves[(size_t)of.cols.height], rows, height, ids, n);
   t1 = now_ns(); g_clock.ns[3] += t1 - t0;
   for (size_t k = 0; k < n; k++) {
     const size_t r = ids[k];
-    if ((int64_t)r >= rows) corrupt("a match outside its row group");
     if (!txid.valid.get((int64_t)r) || !height.valid.get((int64_t)r)) continue;
     Match m;
     m.file = file_index;
@@ -1061,6 +1096,12 @@ struct ResultOwner : cudasp_parquet_result {           // the public struct and 
 
 extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, int n_paths, int threads, cudasp_parquet_result **out) {
   if (!q || !out || n_paths < 0 || (n_paths && !paths)) return stg::fail(q, CUDASP_ERR_ARG, "cudasp_scan_parquet: NULL argument");
+  const uint64_t call_t0 = now_ns();
+  // CUDASP_TRACE: when (ns since the call began) the first / last thread had staged its first row group, finished its scan and
+  // finished collecting its matches
+  std::atomic<uint64_t> first_push_min{~0ull}, first_push_max{0}, scan_done_max{0}, collect_done_max{0};
+  auto at_least = [](std::atomic<uint64_t> &a, uint64_t v) { uint64_t c = a.load(); while (c < v && !a.compare_exchange_weak(c, v)) {} };
+  auto at_most = [](std::atomic<uint64_t> &a, uint64_t v) { uint64_t c = a.load(); while (c > v && !a.compare_exchange_weak(c, v)) {} };
   *out = nullptr;
   std::vector<OpenFile> files((size_t)n_paths);
   struct Item { uint32_t file; size_t group; };
@@ -1087,6 +1128,7 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
   } catch (const Corrupt &c) {
     return stg::fail(q, CUDASP_ERR_IO, ("malformed Parquet file: " + c.what).c_str());
   }
+  const uint64_t opened_ns = now_ns() - call_t0;
   if (threads <= 0) threads = (int)std::max(1u, std::thread::hardware_concurrency());
   threads = (int)std::max<size_t>(1, std::min<size_t>((size_t)threads, items.size()));
   std::vector<std::vector<Match>> found((size_t)threads);
@@ -1096,40 +1138,64 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
   std::string err_msg;
   // One scan per thread, spanning the row groups the thread takes: their rows fill the same pieces (csrc/arrow_ingest.cpp), so
   // the GPUs see whole pieces whatever the row-group size.  A row's number inside the scan is (item << 32) | row in the group.
-  // Only as many threads as there are devices start with ramped-up (small) pieces -- enough for every GPU to start early.
-  const int n_devices = stg::device_count(q);
+  // Every thread starts with ramped-up (small) pieces: measured on one B200 against ramping one thread per device, 10 M rows
+  // 0.172 against 0.182 s, 1 M rows 0.025 against 0.027 s (profiles/r02q_parquet_ramp.txt).
+  int ramped = 1 << 30;
+  if (const char *e = getenv("CUDASP_PARQUET_RAMP")) ramped = atoi(e) < 0 ? 1 << 30 : atoi(e);      // tuning aid: threads that ramp
   auto work = [&](int t) {
     Scratch scratch;
     stg::ColumnScan *scan = nullptr;
     int rc = 0;
     std::string msg;
     try {
-      scan = stg::column_scan_open(q, t < n_devices);
+      scan = stg::column_scan_open(q, t < ramped);
+      bool pushed = false;
+      uint64_t collected = 0;          // matches [0, collected) of the scan are in found[t]
+      std::vector<uint32_t> in_group;
+      // ids [collected, n): runs of one row group each (push order, ascending inside).  Done as the matches come back, between
+      // two row groups, so that little of it is left for the end, when the GPUs have nothing else to do.  A row group whose
+      // matches come back in two parts has its pages read twice.
+      auto collect = [&](const uint64_t *ids, uint64_t n) {
+        for (uint64_t a = collected; a < n;) {
+          const size_t i = (size_t)(ids[a] >> 32);
+          if (i >= items.size()) corrupt("a match outside the files");
+          in_group.clear();
+          for (; a < n && (size_t)(ids[a] >> 32) == i; a++) in_group.push_back((uint32_t)ids[a]);
+          collect_matches(files[items[i].file], items[i].file, items[i].group, in_group.data(), in_group.size(), found[(size_t)t], scratch);      // the row group just pushed is staged: its buffers are free
+        }
+        collected = n;
+      };
       for (;;) {
         const size_t i = next.fetch_add(1);
         if (i >= items.size() || first_rc.load()) break;
         rc = push_row_group(scan, files[items[i].file], items[i].group, (uint64_t)i << 32, scratch);
         if (rc) break;
+        {
+          const uint64_t *ids = nullptr;
+          uint64_t n = 0;
+          stg::column_scan_matches(scan, &ids, &n);
+          collect(ids, n);
+        }
+        if (!pushed) {
+          pushed = true;
+          at_most(first_push_min, now_ns() - call_t0);
+          at_least(first_push_max, now_ns() - call_t0);
+        }
       }
       const uint64_t *ids = nullptr;
       uint64_t n = 0;
       const uint64_t t0 = now_ns();
       const int rc2 = stg::column_scan_finish(scan, &ids, &n);       // also after an error: lets the pieces in flight finish
       g_clock.ns[4] += now_ns() - t0;
+      at_least(scan_done_max, now_ns() - call_t0);
       if (rc) {
         msg = cudasp_last_error(q);
       } else if (rc2) {
         rc = rc2;
         msg = cudasp_last_error(q);
       }
-      std::vector<uint32_t> in_group;
-      for (uint64_t a = 0; !rc && !first_rc.load() && a < n;) {      // ids: grouped by item in push order, ascending inside
-        const size_t i = (size_t)(ids[a] >> 32);
-        if (i >= items.size()) corrupt("a match outside the files");
-        in_group.clear();
-        for (; a < n && (size_t)(ids[a] >> 32) == i; a++) in_group.push_back((uint32_t)ids[a]);
-        collect_matches(files[items[i].file], items[i].file, items[i].group, in_group.data(), in_group.size(), found[(size_t)t], scratch);
-      }
+      if (!rc && !first_rc.load()) collect(ids, n);
+      at_least(collect_done_max, now_ns() - call_t0);
     } catch (const Unsupported &u) {
       rc = CUDASP_ERR_UNSUPPORTED; msg = "Parquet feature outside the fast path: " + u.what;
     } catch (const Corrupt &c) {
@@ -1154,8 +1220,11 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
   }
   if (getenv("CUDASP_TRACE")) {
     fprintf(stderr, "[cudasp] scan_parquet: %llu rows, %d threads; seconds summed over threads: tweak_key %.3f, outputs %.3f, txid %.3f, height %.3f, "
-                    "staging + GPU %.3f\n", (unsigned long long)total_rows, threads, 1e-9 * g_clock.ns[0].exchange(0), 1e-9 * g_clock.ns[1].exchange(0),
-            1e-9 * g_clock.ns[2].exchange(0), 1e-9 * g_clock.ns[3].exchange(0), 1e-9 * g_clock.ns[4].exchange(0));
+                    "staging + GPU %.3f; since the call began: files open %.4f s, first row group staged %.4f .. %.4f s, scans done %.4f s, "
+                    "matches collected %.4f s, threads joined %.4f s\n", (unsigned long long)total_rows, threads, 1e-9 * g_clock.ns[0].exchange(0),
+            1e-9 * g_clock.ns[1].exchange(0), 1e-9 * g_clock.ns[2].exchange(0), 1e-9 * g_clock.ns[3].exchange(0), 1e-9 * g_clock.ns[4].exchange(0),
+            1e-9 * opened_ns, 1e-9 * first_push_min.load(), 1e-9 * first_push_max.load(), 1e-9 * scan_done_max.load(), 1e-9 * collect_done_max.load(),
+            1e-9 * (now_ns() - call_t0));
   }
   if (first_rc.load()) return stg::fail(q, first_rc.load(), err_msg.c_str());
   std::vector<Match> all;

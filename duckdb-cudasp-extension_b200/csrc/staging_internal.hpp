@@ -49,6 +49,9 @@ CSP_HIDDEN ColumnScan *column_scan_open(cudasp_query *q, bool ramp);
 // stages the pair's rows (copied: the arrays may be reused on return); their row numbers count from row_base
 CSP_HIDDEN int column_scan_push(ColumnScan *cs, const ArrowSchema *tweak_schema, const ArrowArray *tweak_key,
                                 const ArrowSchema *outputs_schema, const ArrowArray *outputs, uint64_t row_base);
+// the matching row numbers of the pieces that have come back so far (those whose slot the scan has recycled); the list only
+// grows, in push order; the pointer is valid until the next call on the scan
+CSP_HIDDEN void column_scan_matches(ColumnScan *cs, const uint64_t **rows, uint64_t *n);
 // submits what is left and waits; *rows (owned by the scan) = the matching row numbers, pairs in push order
 CSP_HIDDEN int column_scan_finish(ColumnScan *cs, const uint64_t **rows, uint64_t *n);
 CSP_HIDDEN void column_scan_close(ColumnScan *cs);

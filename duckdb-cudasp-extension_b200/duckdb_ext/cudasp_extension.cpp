@@ -934,8 +934,10 @@ static void CudaspParquetFunction(ClientContext &context, TableFunctionInput &da
 		}
 		idx_t threads = bind.threads > 0 ? (idx_t)bind.threads
 		                                 : MaxValue<idx_t>(1, NumericCast<idx_t>(TaskScheduler::GetScheduler(context).NumberOfThreads()));
-		// every decoder thread has one row group in flight, staged in pieces of at most batch_size rows
-		uint32_t slots = (uint32_t)MinValue<idx_t>(64, (threads + n_dev - 1) / n_dev + 2);
+		// every decoder thread holds one slot while it fills it (pieces of at most batch_size rows, cut across row groups); four
+		// more per device keep copies and batches in flight behind them
+		uint32_t slots = (uint32_t)MinValue<idx_t>(64, (threads + n_dev - 1) / n_dev + 4);
+		const double t_create = NowSec();
 		int rc = cudasp_query_create_ex(const_data_ptr_cast(bind.scan_private_key.data()), const_data_ptr_cast(bind.spend_public_key.data()),
 		                                bind.n_labels ? const_data_ptr_cast(bind.label_keys.data()) : nullptr, bind.n_labels, nullptr, 0,
 		                                (uint32_t)bind.batch_size, 8ull * bind.batch_size, slots, &state.query);
@@ -950,7 +952,12 @@ static void CudaspParquetFunction(ClientContext &context, TableFunctionInput &da
 		for (auto &p : bind.paths) {
 			cpaths.push_back(p.c_str());
 		}
+		const double t_scan = NowSec();
 		rc = cudasp_scan_parquet(state.query, cpaths.data(), (int)cpaths.size(), (int)threads, &state.result);
+		if (getenv("CUDASP_TRACE")) {
+			fprintf(stderr, "[cudasp] cudasp_scan_parquet: query_create %.3f s (%u slots/device, %d devices, %llu threads), scan %.3f s\n",
+			        t_scan - t_create, slots, n_dev, (unsigned long long)threads, NowSec() - t_scan);
+		}
 		if (rc != CUDASP_OK) {
 			const char *msg = cudasp_last_error(state.query);
 			if (rc == CUDASP_ERR_UNSUPPORTED) {
