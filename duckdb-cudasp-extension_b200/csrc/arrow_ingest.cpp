@@ -24,6 +24,8 @@ inline bool bit_set(const uint8_t *bits, int64_t i) { return (bits[i >> 3] >> (i
 
 struct KeyColumn {
   int width = 0;                    // > 0: fixed_size_binary(width); 0: variable (offsets)
+  int64_t stride = 0;               // width > 0 only: bytes from one key to the next; 0 = width (an Arrow array).  Larger for keys
+                                    // read where they lie in a Parquet page (length-prefixed values: stride = width + 4)
   bool large = false;               // variable: 64-bit offsets
   const uint8_t *validity = nullptr;
   const void *offsets = nullptr;
@@ -33,7 +35,7 @@ struct KeyColumn {
 
   bool valid(int64_t i) const { return !validity || bit_set(validity, offset + i); }
   int64_t begin(int64_t i) const {
-    if (width) return (offset + i) * width;
+    if (width) return (offset + i) * (stride ? stride : width);
     return large ? static_cast<const int64_t *>(offsets)[offset + i] : static_cast<const int32_t *>(offsets)[offset + i];
   }
   int64_t size(int64_t i) const { return width ? width : begin(i + 1) - begin(i); }
@@ -138,6 +140,10 @@ class ArrowScanner {
   }
 
   std::vector<uint64_t> matches;
+  // keep_keys: the key of every match, copied from the slot it was staged in when its piece comes back: 64 bytes per match
+  // (a 33-byte key is zero-padded) and its width
+  bool keep_keys = false;
+  std::vector<uint8_t> match_keys, match_key_widths;
 
   int push(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity, int64_t row_validity_offset, uint64_t row_base) {
     int64_t a = 0;
@@ -173,6 +179,7 @@ class ArrowScanner {
     Staging s;
     std::vector<Segment> segs;
     std::vector<uint32_t> rowmap;     // general path: source row - base of its segment, one per staged row of mapped segments
+    int fmt = 0;                      // key format of the piece (set when it is submitted)
   };
 
   cudasp_query *q_;
@@ -191,6 +198,18 @@ class ArrowScanner {
   uint32_t piece_now() const { return cur_; }
   void piece_done() { cur_ = (uint32_t)std::min<uint64_t>(piece_, 2ull * cur_); }
 
+  // cnt keys of w bytes from row `base` on, packed
+  static void copy_keys(uint8_t *dst, const KeyColumn &k, int64_t base, int64_t cnt, int64_t w) {
+    const uint8_t *src = k.data + k.begin(base);
+    if (!k.width || !k.stride || k.stride == k.width) {
+      memcpy(dst, src, (size_t)cnt * w);
+    } else if (w == 64) {
+      for (int64_t i = 0; i < cnt; i++) memcpy(dst + 64 * i, src + k.stride * i, 64);
+    } else {
+      for (int64_t i = 0; i < cnt; i++) memcpy(dst + w * i, src + k.stride * i, (size_t)w);
+    }
+  }
+
   static bool dense_ok(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity) {
     return !row_validity && !k.may_have_nulls && !l.may_have_nulls && !l.child_may_have_nulls;
   }
@@ -208,6 +227,12 @@ class ArrowScanner {
         const Segment &sg = p.segs[g];
         const uint32_t r = id - sg.staged_first;
         matches.push_back(sg.base + (sg.map_first == NO_MAP ? r : p.rowmap[sg.map_first + r]));
+        if (keep_keys) {
+          const size_t w = p.fmt == CUDASP_KEYS_SEC1_33 ? 33 : 64, at = match_keys.size();
+          match_keys.resize(at + 64, 0);
+          memcpy(match_keys.data() + at, p.s.tweaks + (size_t)id * w, w);
+          match_key_widths.push_back((uint8_t)w);
+        }
       }
     }
     stg::release(q_, &p.s);
@@ -260,6 +285,7 @@ class ArrowScanner {
       stg::release(q_, &open_.s);
       return rc;
     }
+    open_.fmt = open_fmt_;
     pending_.push_back(std::move(open_));
     piece_done();
     return 0;
@@ -304,7 +330,7 @@ class ArrowScanner {
       if (rc < 0) return rc;
       if (rc == 1) continue;            // a fresh piece has other room: cut again
       Staging &s = open_.s;
-      memcpy(s.tweaks + (size_t)open_rows_ * w, k.data + k.begin(base), (size_t)cnt * w);
+      copy_keys(s.tweaks + (size_t)open_rows_ * w, k, base, cnt, w);
       // rebase; a malformed batch (offsets going backwards) is refused here: the kernels index outputs[] with these
       const uint32_t first = (uint32_t)open_nout_;
       uint32_t prev = first, bad = 0;
@@ -439,7 +465,7 @@ int parse_pair(cudasp_query *q, const ArrowSchema *tweak_schema, const ArrowArra
 struct csp::staging::ColumnScan {
   cudasp_query *q;
   ArrowScanner sc;
-  ColumnScan(cudasp_query *query, bool ramp) : q(query), sc(query, ramp) {}
+  ColumnScan(cudasp_query *query, bool ramp) : q(query), sc(query, ramp) { sc.keep_keys = true; }
 };
 csp::staging::ColumnScan *csp::staging::column_scan_open(cudasp_query *q, bool ramp) { return new ColumnScan(q, ramp); }
 int csp::staging::column_scan_push(ColumnScan *cs, const ArrowSchema *tweak_schema, const ArrowArray *tweak_key,
@@ -449,16 +475,27 @@ int csp::staging::column_scan_push(ColumnScan *cs, const ArrowSchema *tweak_sche
   int rc = parse_pair(cs->q, tweak_schema, tweak_key, outputs_schema, outputs, &k, &l);
   return rc ? rc : cs->sc.push(k, l, nullptr, 0, row_base);
 }
-void csp::staging::column_scan_matches(ColumnScan *cs, const uint64_t **rows, uint64_t *n) {
+int csp::staging::column_scan_push_keys(ColumnScan *cs, const uint8_t *keys, int64_t stride, int width, int64_t n,
+                                        const ArrowSchema *outputs_schema, const ArrowArray *outputs, uint64_t row_base) {
+  if (!keys || (width != 64 && width != 33) || stride < width || n < 0) return stg::fail(cs->q, CUDASP_ERR_ARG, "column_scan_push_keys: bad key view");
+  KeyColumn k;
+  ListColumn l;
+  k.width = width;
+  k.stride = stride;
+  k.data = keys;
+  k.length = n;
+  int rc = parse_list_column(cs->q, outputs_schema, outputs, &l);
+  if (rc) return rc;
+  if (k.length != l.length) return stg::fail(cs->q, CUDASP_ERR_ARG, "tweak_key and outputs differ in length");
+  return cs->sc.push(k, l, nullptr, 0, row_base);
+}
+void csp::staging::column_scan_matches(ColumnScan *cs, const uint64_t **rows, uint64_t *n, const uint8_t **keys64, const uint8_t **key_widths) {
   *rows = cs->sc.matches.data();
   *n = cs->sc.matches.size();
+  if (keys64) *keys64 = cs->sc.match_keys.data();
+  if (key_widths) *key_widths = cs->sc.match_key_widths.data();
 }
-int csp::staging::column_scan_finish(ColumnScan *cs, const uint64_t **rows, uint64_t *n) {
-  int rc = cs->sc.drain();
-  *rows = cs->sc.matches.data();
-  *n = cs->sc.matches.size();
-  return rc;
-}
+int csp::staging::column_scan_finish(ColumnScan *cs) { return cs->sc.drain(); }
 void csp::staging::column_scan_close(ColumnScan *cs) { delete cs; }
 
 extern "C" {

@@ -426,6 +426,43 @@ struct HybridDecoder {
       }
     }
   }
+  // One-bit values (repetition levels of a one-level list): calls f(i) for every i in [0, n) whose value is 0 -- where a row
+  // starts -- without expanding the levels: an RLE run is a loop or a skip, a bit-packed run is scanned 64 levels at a time.
+  template <class F>
+  void for_each_zero(uint64_t n, F f) {
+    if (bw != 1) corrupt("hybrid: one-bit levels expected");
+    uint64_t at = 0;
+    while (at < n) {
+      if (rle_left == 0 && packed_left == 0) next_run();
+      if (rle_left) {
+        const uint64_t k = std::min(n - at, rle_left);
+        if (!(rle_value & 1)) for (uint64_t i = 0; i < k; i++) f(at + i);
+        at += k; rle_left -= k;
+      } else {
+        const uint64_t k = std::min(n - at, packed_left);
+        uint64_t i = 0;
+        while (i < k) {
+          const uint64_t bit = bitpos + i;
+          const uint8_t *q = p + (bit >> 3);
+          uint64_t w = 0;
+          const size_t avail = (size_t)(end - q);
+          memcpy(&w, q, avail < 8 ? avail : 8);
+          const unsigned sh = (unsigned)(bit & 7);
+          const uint64_t take = std::min<uint64_t>(k - i, 64 - sh);       // levels of this load that belong to the run
+          uint64_t z = ~(w >> sh);
+          if (take < 64) z &= (1ull << take) - 1;
+          while (z) {
+            f(at + i + (uint64_t)__builtin_ctzll(z));
+            z &= z - 1;
+          }
+          i += take;
+        }
+        bitpos += k;
+        at += k; packed_left -= k;
+        if (packed_left == 0) { p += (bitpos + 7) / 8; bitpos = 0; }
+      }
+    }
+  }
   // true (and consumes them) when the next n values are one RLE run of `value`: the all-valid fast path
   bool all_equal(uint64_t n, uint32_t value) {
     if (rle_left == 0 && packed_left == 0) {
@@ -708,12 +745,60 @@ void page_blobs(const ChunkReader &cr, const Page &pg, int64_t n_present, Put pu
   }
 }
 
-// want / n_want: only the pages that hold these rows (ascending) are decoded; every other row reads as an empty value
-void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf, int64_t rows, BlobColumn &out, size_t size_hint,
-                        const uint32_t *want = nullptr, size_t n_want = 0) {
+// One data page of a flat BYTE_ARRAY / FIXED_LEN_BYTE_ARRAY column, appended to `out` as rows [row, row + pg.num_values): the
+// caller has sized out.offsets and initialised out.valid for them.
+void decode_blob_page(const ChunkReader &cr, const Page &pg, const Leaf &lf, BlobColumn &out, int64_t row, std::vector<uint32_t> &defs) {
+  const int64_t n = pg.num_values;
+  int64_t present = n;
+  bool all_valid = true;
+  if (lf.max_def) {
+    HybridDecoder d;
+    d.init(pg.def, pg.def_end, 1);
+    if (!d.all_equal((uint64_t)n, 1)) {
+      d.init(pg.def, pg.def_end, 1);
+      defs.resize((size_t)n);
+      d.get(defs.data(), (uint64_t)n);
+      present = 0;
+      for (int64_t i = 0; i < n; i++) present += defs[i] != 0;
+      all_valid = present == n;
+    }
+  }
+  int64_t i = 0;      // value slot within the page
+  if (all_valid && pg.encoding == E_PLAIN && lf.type == T_FLBA) {
+    // fixed-size values, no NULLs: the page's value area IS the column data
+    const size_t w = (size_t)lf.type_length, bytes = w * (size_t)n;
+    if (lf.type_length <= 0 || (size_t)(pg.values_end - pg.values) < bytes) corrupt("page: fixed-length values past the end");
+    const size_t base = out.data.size();
+    if (base + bytes > 0x7fffffffull) unsupported("more than 2 GiB of " + lf.path[0] + " in one row group");
+    memcpy(out.data.grow(bytes), pg.values, bytes);
+    int32_t *o = out.offsets.data() + row + 1;
+    for (int64_t k = 0; k < n; k++) o[k] = (int32_t)(base + w * (size_t)(k + 1));
+    i = n;
+  } else {
+    page_blobs(cr, pg, present, [&](const uint8_t *p, uint32_t len) {
+      if (!all_valid) {
+        while (defs[(size_t)i] == 0) { out.valid.clear(row + i); out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size(); i++; }
+      }
+      uint8_t *dst = out.data.grow(len);
+      if (len == 64) memcpy(dst, p, 64); else if (len == 32) memcpy(dst, p, 32); else memcpy(dst, p, len);
+      out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size();
+      i++;
+    });
+    if (out.data.size() > 0x7fffffffull) unsupported("more than 2 GiB of " + lf.path[0] + " in one row group");
+  }
+  for (; i < n; i++) { out.valid.clear(row + i); out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size(); }   // trailing NULLs
+}
+
+void check_blob_leaf(const ChunkMeta &cm, const Leaf &lf) {
   if (lf.type != T_BYTE_ARRAY && lf.type != T_FLBA) unsupported("column " + lf.path[0] + " is not BYTE_ARRAY / FIXED_LEN_BYTE_ARRAY");
   if (lf.max_rep != 0 || lf.max_def > 1) unsupported("column " + lf.path[0] + " is nested");
   if (lf.type == T_FLBA && cm.dict_page_offset > 0 && lf.type_length <= 0) corrupt("fixed-length column without a length");
+}
+
+// want / n_want: only the pages that hold these rows (ascending) are decoded; every other row reads as an empty value
+void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf, int64_t rows, BlobColumn &out, size_t size_hint,
+                        const uint32_t *want = nullptr, size_t n_want = 0) {
+  check_blob_leaf(cm, lf);
   ChunkReader cr(f, cm, lf, want, n_want);
   out.offsets.resize((size_t)rows + 1);
   out.offsets[0] = 0;
@@ -732,50 +817,46 @@ void decode_blob_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
     if (pg.skipped) {
       const int32_t at = (int32_t)out.data.size();
       for (int64_t k = 0; k < n; k++) out.offsets[(size_t)(row + k) + 1] = at;
-      row += n;
-      continue;
-    }
-    int64_t present = n;
-    bool all_valid = true;
-    if (lf.max_def) {
-      HybridDecoder d;
-      d.init(pg.def, pg.def_end, 1);
-      if (!d.all_equal((uint64_t)n, 1)) {
-        d.init(pg.def, pg.def_end, 1);
-        defs.resize((size_t)n);
-        d.get(defs.data(), (uint64_t)n);
-        present = 0;
-        for (int64_t i = 0; i < n; i++) present += defs[i] != 0;
-        all_valid = present == n;
-      }
-    }
-    int64_t i = 0;      // value slot within the page
-    if (all_valid && pg.encoding == E_PLAIN && lf.type == T_FLBA) {
-      // fixed-size values, no NULLs: the page's value area IS the column data
-      const size_t w = (size_t)lf.type_length, bytes = w * (size_t)n;
-      if (lf.type_length <= 0 || (size_t)(pg.values_end - pg.values) < bytes) corrupt("page: fixed-length values past the end");
-      const size_t base = out.data.size();
-      if (base + bytes > 0x7fffffffull) unsupported("more than 2 GiB of " + lf.path[0] + " in one row group");
-      memcpy(out.data.grow(bytes), pg.values, bytes);
-      int32_t *o = out.offsets.data() + row + 1;
-      for (int64_t k = 0; k < n; k++) o[k] = (int32_t)(base + w * (size_t)(k + 1));
-      i = n;
     } else {
-      page_blobs(cr, pg, present, [&](const uint8_t *p, uint32_t len) {
-        if (!all_valid) {
-          while (defs[(size_t)i] == 0) { out.valid.clear(row + i); out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size(); i++; }
-        }
-        uint8_t *dst = out.data.grow(len);
-        if (len == 64) memcpy(dst, p, 64); else if (len == 32) memcpy(dst, p, 32); else memcpy(dst, p, len);
-        out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size();
-        i++;
-      });
-      if (out.data.size() > 0x7fffffffull) unsupported("more than 2 GiB of " + lf.path[0] + " in one row group");
+      decode_blob_page(cr, pg, lf, out, row, defs);
     }
-    for (; i < n; i++) { out.valid.clear(row + i); out.offsets[(size_t)(row + i) + 1] = (int32_t)out.data.size(); }   // trailing NULLs
     row += n;
   }
   if (row != rows) corrupt("column " + lf.path[0] + ": fewer values than the row group has rows");
+}
+
+// A data page whose keys can be staged from where they lie: no NULLs, PLAIN, every value 64 or 33 bytes long.  Fixed-length
+// values are packed (stride = width); BYTE_ARRAY values carry a 4-byte length each (stride = width + 4), all checked here.
+bool page_key_view(const Page &pg, const Leaf &lf, const uint8_t **keys, int64_t *stride, int *width) {
+  const int64_t n = pg.num_values;
+  if (n <= 0 || pg.encoding != E_PLAIN) return false;
+  if (lf.max_def) {
+    HybridDecoder d;
+    d.init(pg.def, pg.def_end, 1);
+    if (!d.all_equal((uint64_t)n, 1)) return false;
+  }
+  const int64_t room = (int64_t)(pg.values_end - pg.values);
+  if (lf.type == T_FLBA) {
+    const int64_t w = lf.type_length;
+    if ((w != 64 && w != 33) || room < w * n) return false;
+    *keys = pg.values; *stride = w; *width = (int)w;
+    return true;
+  }
+  if (room < 4) return false;
+  uint32_t len0;
+  memcpy(&len0, pg.values, 4);
+  if ((len0 != 64 && len0 != 33) || room < (int64_t)(len0 + 4) * n) return false;
+  const int64_t st = (int64_t)len0 + 4;
+  uint32_t diff = 0;
+  const uint8_t *q = pg.values;
+  for (int64_t i = 0; i < n; i++, q += st) {
+    uint32_t len;
+    memcpy(&len, q, 4);
+    diff |= len ^ len0;
+  }
+  if (diff) return false;
+  *keys = pg.values + 4; *stride = st; *width = (int)len0;
+  return true;
 }
 
 void decode_int32_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf, int64_t rows, Int32Column &out,
@@ -856,15 +937,15 @@ void decode_list_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
   const int def_bw = bits_for(lf.max_def);
   while (cr.next(pg)) {
     const int64_t n = pg.num_values;
-    reps.resize((size_t)n);
-    defs.resize((size_t)n);
     HybridDecoder r, d;
     r.init(pg.rep, pg.rep_end, 1);
-    r.get(reps.data(), (uint64_t)n);
     d.init(pg.def, pg.def_end, def_bw);
     const bool all_present = d.all_equal((uint64_t)n, (uint32_t)lf.max_def);
     int64_t present = n;
     if (!all_present) {
+      reps.resize((size_t)n);
+      defs.resize((size_t)n);
+      r.get(reps.data(), (uint64_t)n);
       d.init(pg.def, pg.def_end, def_bw);
       d.get(defs.data(), (uint64_t)n);
       present = 0;
@@ -895,12 +976,10 @@ void decode_list_column(const MappedFile &f, const ChunkMeta &cm, const Leaf &lf
       uint8_t *dst = out.value_bytes.grow((size_t)n * 8);
       if (dict) { for (int64_t k = 0; k < n; k++) memcpy(dst + 8 * k, cr.dict.data + 8 * (size_t)idx[(size_t)k], 8); }
       else memcpy(dst, q, (size_t)n * 8);
-      for (int64_t i = 0; i < n; i++) {
-        if (reps[(size_t)i] == 0) {
-          if (row >= 0) out.offsets[(size_t)row + 1] = (int32_t)(base + (size_t)i);
-          if (++row >= rows) corrupt("column " + lf.path[0] + ": more rows than the row group has");
-        }
-      }
+      r.for_each_zero((uint64_t)n, [&](uint64_t i) {
+        if (row >= 0) out.offsets[(size_t)row + 1] = (int32_t)(base + (size_t)i);
+        if (++row >= rows) corrupt("column " + lf.path[0] + ": more rows than the row group has");
+      });
       if (row < 0) corrupt("column " + lf.path[0] + ": the row group starts inside a row");
       continue;
     }
@@ -1019,11 +1098,12 @@ struct Scratch {               // one per decoder thread: the decoded columns of
   BlobColumn txid, key;
   Int32Column height;
   ListColumn outs;
-  std::vector<uint64_t> ids;
+  std::vector<uint32_t> defs;
 };
-// Decodes tweak_key and outputs of one row group and stages its rows into the thread's scan; their row numbers count from
-// row_base.  txid and height are NOT decoded here: the scan does not need them, so the GPUs get their first rows a third
-// sooner; collect_matches() decodes them for the (few) row groups that held a match.
+// Stages the rows of one row group into the thread's scan; their row numbers count from row_base.  outputs is decoded for the
+// whole row group; tweak_key goes page by page: a page of plain 64- or 33-byte values without NULLs is staged from where it
+// lies in the file mapping (no intermediate copy), any other page is decoded first.  txid and height are NOT read here: the
+// scan does not need them; collect_matches() reads the pages that hold a matching row.
 int push_row_group(stg::ColumnScan *scan, const OpenFile &of, size_t g, uint64_t row_base, Scratch &sc) {
   const RowGroupMeta &rg = of.meta.row_groups[g];
   const int64_t rows = rg.num_rows;
@@ -1032,8 +1112,6 @@ int push_row_group(stg::ColumnScan *scan, const OpenFile &of, size_t g, uint64_t
   BlobColumn &key = sc.key;
   ListColumn &outs = sc.outs;
   uint64_t t0 = now_ns(), t1;
-  decode_blob_column(of.map, rg.cols[(size_t)of.cols.tweak], of.meta.leaves[(size_t)of.cols.tweak], rows, key, 64);
-  t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
   decode_list_column(of.map, rg.cols[(size_t)of.cols.outputs], of.meta.leaves[(size_t)of.cols.outputs], rows, outs);
   t1 = now_ns(); g_clock.ns[1] += t1 - t0; t0 = t1;
 
@@ -1044,30 +1122,61 @@ int push_row_group(stg::ColumnScan *scan, const OpenFile &of, size_t g, uint64_t
   os.format = "+l"; os.name = "outputs"; os.flags = ARROW_FLAG_NULLABLE; os.n_children = 1; os.children = os_children;
   ArrowArray ta{}, oa{}, ca{};
   ArrowArray *oa_children[1] = {&ca};
-  const void *tb[3] = {key.valid.nulls ? key.valid.bits.data() : nullptr, key.offsets.data(), key.data.empty() ? (const void *)"" : (const void *)key.data.data()};
-  ta.length = rows; ta.null_count = key.valid.nulls; ta.n_buffers = 3; ta.buffers = tb;
   const void *cb[2] = {outs.child_valid.nulls ? outs.child_valid.bits.data() : nullptr, outs.n_values() ? (const void *)outs.values() : (const void *)""};
   ca.length = (int64_t)outs.n_values(); ca.null_count = outs.child_valid.nulls; ca.n_buffers = 2; ca.buffers = cb;
   const void *ob[2] = {outs.valid.nulls ? outs.valid.bits.data() : nullptr, outs.offsets.data()};
-  oa.length = rows; oa.null_count = outs.valid.nulls; oa.n_buffers = 2; oa.buffers = ob; oa.n_children = 1; oa.children = oa_children;
-  const int rc = stg::column_scan_push(scan, &ts, &ta, &os, &oa, row_base);
-  t1 = now_ns(); g_clock.ns[4] += t1 - t0;
-  return rc;
+  oa.null_count = outs.valid.nulls; oa.n_buffers = 2; oa.buffers = ob; oa.n_children = 1; oa.children = oa_children;
+
+  const ChunkMeta &kcm = rg.cols[(size_t)of.cols.tweak];
+  const Leaf &klf = of.meta.leaves[(size_t)of.cols.tweak];
+  check_blob_leaf(kcm, klf);
+  ChunkReader cr(of.map, kcm, klf);
+  Page pg;
+  int64_t row = 0;
+  while (cr.next(pg)) {
+    const int64_t n = pg.num_values;
+    if (row + n > rows) corrupt("column " + klf.path[0] + ": more values than the row group has rows");
+    oa.offset = row;                      // this page's rows of the outputs column (an Arrow slice)
+    oa.length = n;
+    const uint8_t *keys = nullptr;
+    int64_t stride = 0;
+    int width = 0;
+    int rc;
+    if (page_key_view(pg, klf, &keys, &stride, &width)) {
+      t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
+      rc = stg::column_scan_push_keys(scan, keys, stride, width, n, &os, &oa, row_base + (uint64_t)row);
+    } else {
+      key.offsets.resize((size_t)n + 1);
+      key.offsets[0] = 0;
+      key.data.clear();
+      key.valid.init(n);
+      decode_blob_page(cr, pg, klf, key, 0, sc.defs);
+      const void *tb[3] = {key.valid.nulls ? key.valid.bits.data() : nullptr, key.offsets.data(), key.data.empty() ? (const void *)"" : (const void *)key.data.data()};
+      ta.length = n; ta.null_count = key.valid.nulls; ta.n_buffers = 3; ta.buffers = tb;
+      t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
+      rc = stg::column_scan_push(scan, &ts, &ta, &os, &oa, row_base + (uint64_t)row);
+    }
+    t1 = now_ns(); g_clock.ns[4] += t1 - t0; t0 = t1;
+    if (rc) return rc;
+    row += n;
+  }
+  if (row != rows) corrupt("column " + klf.path[0] + ": fewer values than the row group has rows");
+  return 0;
 }
 
-// The matching rows ids[0..n) of one row group (ascending) -> Match records.  A row with a NULL txid or height, which the
-// reference drops before the GPU (src/cudasp_extension.cu:195-197), is dropped here instead: the same result set.
-void collect_matches(const OpenFile &of, uint32_t file_index, size_t g, const uint32_t *ids, size_t n, std::vector<Match> &matches, Scratch &sc) {
+// The matching rows ids[0..n) of one row group (ascending) -> Match records; their keys come from the scan (keys64, 64 bytes
+// a match, and widths).  A row with a NULL txid or height, which the reference drops before the GPU
+// (src/cudasp_extension.cu:195-197), is dropped here instead: the same result set.
+void collect_matches(const OpenFile &of, uint32_t file_index, size_t g, const uint32_t *ids, size_t n, const uint8_t *keys64,
+                     const uint8_t *widths, std::vector<Match> &matches, Scratch &sc) {
   const RowGroupMeta &rg = of.meta.row_groups[g];
   const int64_t rows = rg.num_rows;
-  BlobColumn &txid = sc.txid, &key = sc.key;
+  BlobColumn &txid = sc.txid;
   Int32Column &height = sc.height;
   uint64_t t0 = now_ns(), t1;
   for (size_t k = 0; k < n; k++)
     if ((int64_t)ids[k] >= rows || (k && ids[k] <= ids[k - 1])) corrupt("a match outside its row group");
   // only the pages that hold a matching row are read (ChunkReader::want)
-  decode_blob_column(of.map, rg.cols[(size_t)of.cols.tweak], of.meta.leaves[(size_t)of.cols.tweak], rows, key, 64, ids, n);
-  t1 = now_ns(); g_clock.ns[0] += t1 - t0; t0 = t1;
   decode_blob_column(of.map, rg.cols[(size_t)of.cols.txid], of.meta.leaves[(size_t)of.cols.txid], rows, txid, 32, ids, n);
   t1 = now_ns(); g_clock.ns[2] += t1 - t0; t0 = t1;
   decode_int32_column(of.map, rg.cols[(size_t)of.cols.height], of.meta.leaves[(size_t)of.cols.height], rows, height, ids, n);
@@ -1080,7 +1189,7 @@ void collect_matches(const OpenFile &of, uint32_t file_index, size_t g, const ui
     m.row = (uint64_t)of.row_base[g] + r;
     m.height = height.values[r];
     m.txid.assign(reinterpret_cast<const char *>(txid.data.data()) + txid.offsets[r], (size_t)(txid.offsets[r + 1] - txid.offsets[r]));
-    m.key.assign(reinterpret_cast<const char *>(key.data.data()) + key.offsets[r], (size_t)(key.offsets[r + 1] - key.offsets[r]));
+    m.key.assign(reinterpret_cast<const char *>(keys64) + 64 * k, (size_t)widths[k]);
     matches.push_back(std::move(m));
   }
 }
@@ -1155,13 +1264,19 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
       // ids [collected, n): runs of one row group each (push order, ascending inside).  Done as the matches come back, between
       // two row groups, so that little of it is left for the end, when the GPUs have nothing else to do.  A row group whose
       // matches come back in two parts has its pages read twice.
-      auto collect = [&](const uint64_t *ids, uint64_t n) {
+      auto collect = [&]() {
+        const uint64_t *ids = nullptr;
+        const uint8_t *keys64 = nullptr, *widths = nullptr;
+        uint64_t n = 0;
+        stg::column_scan_matches(scan, &ids, &n, &keys64, &widths);
         for (uint64_t a = collected; a < n;) {
+          const uint64_t a0 = a;
           const size_t i = (size_t)(ids[a] >> 32);
           if (i >= items.size()) corrupt("a match outside the files");
           in_group.clear();
           for (; a < n && (size_t)(ids[a] >> 32) == i; a++) in_group.push_back((uint32_t)ids[a]);
-          collect_matches(files[items[i].file], items[i].file, items[i].group, in_group.data(), in_group.size(), found[(size_t)t], scratch);      // the row group just pushed is staged: its buffers are free
+          collect_matches(files[items[i].file], items[i].file, items[i].group, in_group.data(), in_group.size(), keys64 + 64 * a0, widths + a0,
+                          found[(size_t)t], scratch);
         }
         collected = n;
       };
@@ -1170,22 +1285,15 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
         if (i >= items.size() || first_rc.load()) break;
         rc = push_row_group(scan, files[items[i].file], items[i].group, (uint64_t)i << 32, scratch);
         if (rc) break;
-        {
-          const uint64_t *ids = nullptr;
-          uint64_t n = 0;
-          stg::column_scan_matches(scan, &ids, &n);
-          collect(ids, n);
-        }
+        collect();
         if (!pushed) {
           pushed = true;
           at_most(first_push_min, now_ns() - call_t0);
           at_least(first_push_max, now_ns() - call_t0);
         }
       }
-      const uint64_t *ids = nullptr;
-      uint64_t n = 0;
       const uint64_t t0 = now_ns();
-      const int rc2 = stg::column_scan_finish(scan, &ids, &n);       // also after an error: lets the pieces in flight finish
+      const int rc2 = stg::column_scan_finish(scan);       // also after an error: lets the pieces in flight finish
       g_clock.ns[4] += now_ns() - t0;
       at_least(scan_done_max, now_ns() - call_t0);
       if (rc) {
@@ -1194,7 +1302,7 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
         rc = rc2;
         msg = cudasp_last_error(q);
       }
-      if (!rc && !first_rc.load()) collect(ids, n);
+      if (!rc && !first_rc.load()) collect();
       at_least(collect_done_max, now_ns() - call_t0);
     } catch (const Unsupported &u) {
       rc = CUDASP_ERR_UNSUPPORTED; msg = "Parquet feature outside the fast path: " + u.what;

@@ -49,11 +49,16 @@ CSP_HIDDEN ColumnScan *column_scan_open(cudasp_query *q, bool ramp);
 // stages the pair's rows (copied: the arrays may be reused on return); their row numbers count from row_base
 CSP_HIDDEN int column_scan_push(ColumnScan *cs, const ArrowSchema *tweak_schema, const ArrowArray *tweak_key,
                                 const ArrowSchema *outputs_schema, const ArrowArray *outputs, uint64_t row_base);
-// the matching row numbers of the pieces that have come back so far (those whose slot the scan has recycled); the list only
-// grows, in push order; the pointer is valid until the next call on the scan
-CSP_HIDDEN void column_scan_matches(ColumnScan *cs, const uint64_t **rows, uint64_t *n);
-// submits what is left and waits; *rows (owned by the scan) = the matching row numbers, pairs in push order
-CSP_HIDDEN int column_scan_finish(ColumnScan *cs, const uint64_t **rows, uint64_t *n);
+// the same with the keys read where they lie: n keys of `width` (64 or 33) bytes, `stride` bytes apart (PLAIN Parquet pages:
+// fixed-length values stride = width, length-prefixed ones stride = width + 4), no NULLs; outputs as above (n rows: a slice)
+CSP_HIDDEN int column_scan_push_keys(ColumnScan *cs, const uint8_t *keys, int64_t stride, int width, int64_t n,
+                                     const ArrowSchema *outputs_schema, const ArrowArray *outputs, uint64_t row_base);
+// The matching row numbers of the pieces that have come back so far (those whose slot the scan has recycled); the list only
+// grows, in push order.  keys64 / key_widths (may be NULL): the key of match i = keys64[64 * i ..][0 .. key_widths[i]), copied
+// from the staging slot -- the caller need not keep or re-read its key column.  Valid until the next call on the scan.
+CSP_HIDDEN void column_scan_matches(ColumnScan *cs, const uint64_t **rows, uint64_t *n, const uint8_t **keys64, const uint8_t **key_widths);
+// submits what is left and waits for every piece; column_scan_matches() then holds all matches
+CSP_HIDDEN int column_scan_finish(ColumnScan *cs);
 CSP_HIDDEN void column_scan_close(ColumnScan *cs);
 
 }  // namespace staging

@@ -209,3 +209,36 @@ def test_pieces_span_row_groups(P, tmp_path):
     assert res[0] == 4000
     assert [(g[0],) + g[1:] for g in res[1]] == [(0,) + e for e in expect] + [(1,) + e for e in expect]
     assert st["rows"] == 4000 and st["submits"] == -(-4000 // 128)         # 32 pieces, not 80
+
+
+@pytest.mark.parametrize("key_type", [pa.binary(), pa.binary(64), pa.binary(33)])
+@pytest.mark.parametrize("settings", [0, 2, 3, 5])
+def test_dense_pages_staged_where_they_lie(P, tmp_path, key_type, settings):
+    """The fast paths: pages of plain 64- / 33-byte keys without NULLs are staged straight from the file mapping (fixed-length
+    values packed, BYTE_ARRAY values behind their 4-byte lengths), and pages of outputs in which every level entry is a value
+    find their row starts by scanning the one-bit repetition levels -- RLE runs of 0 (one-element lists), RLE runs of 1 (one
+    long list) and bit-packed stretches."""
+    rng = np.random.default_rng(500 + settings)
+    w = 33 if key_type == pa.binary(33) else 64
+    lens = np.concatenate([np.ones(3000, np.int64), [700], rng.integers(1, 10, 4000), np.ones(77, np.int64), [2, 1, 300], rng.integers(1, 4, 2500)])
+    n = len(lens)
+    keys = rng.integers(0, 256, (n, w), dtype=np.uint8)
+    want = keys[:, 1:9].copy().view("<i8").reshape(n)
+    off = np.zeros(n + 1, np.int64)
+    off[1:] = np.cumsum(lens)
+    vals = rng.integers(-2**62, 2**62, int(off[-1]), dtype=np.int64)
+    hit = np.flatnonzero(rng.random(n) < 0.1)
+    vals[off[hit] + rng.integers(0, 1 << 30, len(hit)) % lens[hit]] = want[hit]
+    txid = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    height = (700000 + np.arange(n)).astype(np.int32)
+    tbl = pa.table({"txid": pa.FixedSizeBinaryArray.from_buffers(pa.binary(32), n, [None, pa.py_buffer(txid.tobytes())]).cast(pa.binary()),
+                    "height": pa.array(height),
+                    "tweak_key": pa.FixedSizeBinaryArray.from_buffers(pa.binary(w), n, [None, pa.py_buffer(keys.tobytes())]).cast(key_type),
+                    "outputs": pa.ListArray.from_arrays(pa.array(off.astype(np.int32)), pa.array(vals))})
+    path = str(tmp_path / "dense.parquet")
+    pq.write_table(tbl, path, row_group_size=4100, **WRITER_SETTINGS[settings])
+    st = {}
+    rc, res = P([path], piece=1000, cap_rows=1000, cap_outputs=2000, stats=st)
+    assert rc == 0, res
+    assert res[0] == n and st["rows"] == n
+    assert [(g[1], g[2], g[3], g[4]) for g in res[1]] == [(int(i), txid[i].tobytes(), int(height[i]), keys[i].tobytes()) for i in hit]
