@@ -14,6 +14,9 @@
 
 #include "../../include/cudasp_arrow.h"
 #include "staging_internal.hpp"
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 namespace {
 
@@ -204,6 +207,20 @@ class ArrowScanner {
     if (!k.width || !k.stride || k.stride == k.width) {
       memcpy(dst, src, (size_t)cnt * w);
     } else if (w == 64) {
+#if defined(__SSE2__)
+      if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        // keys lifted out of a Parquet page: written once, read next by the DMA engine -- streaming stores keep them out of the
+        // caches (the same finding as the DuckDB extension's CopyStreaming)
+        for (int64_t i = 0; i < cnt; i++) {
+          const __m128i *a = reinterpret_cast<const __m128i *>(src + k.stride * i);
+          __m128i *d = reinterpret_cast<__m128i *>(dst + 64 * i);
+          const __m128i v0 = _mm_loadu_si128(a), v1 = _mm_loadu_si128(a + 1), v2 = _mm_loadu_si128(a + 2), v3 = _mm_loadu_si128(a + 3);
+          _mm_stream_si128(d, v0); _mm_stream_si128(d + 1, v1); _mm_stream_si128(d + 2, v2); _mm_stream_si128(d + 3, v3);
+        }
+        _mm_sfence();
+        return;
+      }
+#endif
       for (int64_t i = 0; i < cnt; i++) memcpy(dst + 64 * i, src + k.stride * i, 64);
     } else {
       for (int64_t i = 0; i < cnt; i++) memcpy(dst + w * i, src + k.stride * i, (size_t)w);
