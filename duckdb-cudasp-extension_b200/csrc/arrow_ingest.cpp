@@ -6,6 +6,7 @@
 //   dense   : no NULL keys / lists / children in sight and one key width -> memcpy(keys), rebase(offsets), memcpy(values)
 //   general : row by row with the reference's NULL rules, rows compacted, a row map kept to translate ids back
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <deque>
@@ -115,6 +116,10 @@ int parse_list_column(cudasp_query *q, const ArrowSchema *sc, const ArrowArray *
   return 0;
 }
 
+inline uint64_t now_ns() {
+  return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 int format_of(int64_t key_size) {
   return key_size == 64 ? CUDASP_KEYS_XY64 : key_size == 33 ? CUDASP_KEYS_SEC1_33 : -1;
 }
@@ -147,6 +152,7 @@ class ArrowScanner {
   // (a 33-byte key is zero-padded) and its width
   bool keep_keys = false;
   std::vector<uint8_t> match_keys, match_key_widths;
+  uint64_t wait_ns = 0;             // time spent waiting for the devices: for a piece to come back, or for a free slot
 
   int push(const KeyColumn &k, const ListColumn &l, const uint8_t *row_validity, int64_t row_validity_offset, uint64_t row_base) {
     int64_t a = 0;
@@ -235,7 +241,9 @@ class ArrowScanner {
     Pending p = std::move(pending_.front());
     pending_.pop_front();
     uint32_t n = 0;
+    const uint64_t t0 = now_ns();
     int rc = stg::finish(q_, &p.s, &n);
+    wait_ns += now_ns() - t0;
     if (!rc) {
       size_t g = 0;                   // ids ascend: the segment cursor only moves forward
       for (uint32_t i = 0; i < n; i++) {
@@ -264,7 +272,9 @@ class ArrowScanner {
         rc = collect_front();
         if (rc) return rc;
       } else {
+        const uint64_t t0 = now_ns();
         rc = stg::acquire(q_, s, true);
+        wait_ns += now_ns() - t0;
         return rc < 0 ? rc : 0;
       }
     }
@@ -513,6 +523,7 @@ void csp::staging::column_scan_matches(ColumnScan *cs, const uint64_t **rows, ui
   if (key_widths) *key_widths = cs->sc.match_key_widths.data();
 }
 int csp::staging::column_scan_finish(ColumnScan *cs) { return cs->sc.drain(); }
+uint64_t csp::staging::column_scan_wait_ns(ColumnScan *cs) { return cs->sc.wait_ns; }
 void csp::staging::column_scan_close(ColumnScan *cs) { delete cs; }
 
 extern "C" {

@@ -59,6 +59,8 @@ CSP_HIDDEN int column_scan_push_keys(ColumnScan *cs, const uint8_t *keys, int64_
 CSP_HIDDEN void column_scan_matches(ColumnScan *cs, const uint64_t **rows, uint64_t *n, const uint8_t **keys64, const uint8_t **key_widths);
 // submits what is left and waits for every piece; column_scan_matches() then holds all matches
 CSP_HIDDEN int column_scan_finish(ColumnScan *cs);
+// nanoseconds the scan has spent waiting for the devices (a piece to come back, a slot to come free): tracing
+CSP_HIDDEN uint64_t column_scan_wait_ns(ColumnScan *cs);
 CSP_HIDDEN void column_scan_close(ColumnScan *cs);
 
 }  // namespace staging

@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--details", action="store_true", help="details := true (one result row per found output)")
     ap.add_argument("--in-memory", action="store_true", help="load the table into a DuckDB table first (no Parquet decode in the timed query)")
     ap.add_argument("--native", action="store_true", help="also time cudasp_scan_parquet(paths, ...): the library's own page decoders instead of DuckDB's read_parquet")
+    ap.add_argument("--native-threads", type=str, default="", help="with --native: also time cudasp_scan_parquet with threads := N for every N of this comma list")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "both"], help="which extension runs the SQL (same file, same query)")
     a = ap.parse_args()
     import numpy as np
@@ -82,6 +83,9 @@ def main():
             paths = "[%s]" % ", ".join(["'%s'" % path] * a.replicate)
             nq = "SELECT count(*) FROM cudasp_scan_parquet(%s, %s, %s, %s, batch_size := %d);" % (paths, blob(T["sk"]), blob(T["spend"]), labels, a.batch)
             native = nq + "\n" + nq + "\n" + nq + "\n"
+            for nt in [int(x) for x in a.native_threads.split(",") if x]:
+                nq2 = nq.replace("batch_size :=", "threads := %d, batch_size :=" % nt)
+                native += nq2 + "\n" + nq2 + "\n" + nq2 + "\n"
         sql = pre + ".timer on\n" + scan + "\n" + scan + "\n" + plain + "\n" + native + "SELECT current_setting('threads');\n"
         p = subprocess.run([exe, "-csv", "-noheader"], input=sql, capture_output=True, text=True, timeout=1800)
         if os.environ.get("CUDASP_TRACE"):
@@ -99,6 +103,11 @@ def main():
         if native and len(times) >= 6 and len(vals) >= 6:
             res["native_parquet"] = {"scan_s_first": times[3], "scan_s_warm": min(times[4:6]), "rows_per_s_warm": rows / min(times[4:6]),
                                      "matches_ok": all(int(v) == want for v in vals[3:6])}
+            for j, nt in enumerate([int(x) for x in a.native_threads.split(",") if x]):
+                lo = 6 + 3 * j
+                if len(times) >= lo + 3 and len(vals) >= lo + 3:
+                    res["native_parquet_threads_%d" % nt] = {"scan_s_warm": min(times[lo + 1:lo + 3]), "rows_per_s_warm": rows / min(times[lo + 1:lo + 3]),
+                                                            "matches_ok": all(int(v) == want for v in vals[lo:lo + 3])}
         print(json.dumps(res))
     try:
         os.remove(path)
