@@ -105,8 +105,15 @@ struct Thrift {
     elem_type = h & 0x0f;
     n = h >> 4;
     if (n == 15) n = varint();
+    if (n > (uint64_t)(end - p)) corrupt("thrift: list longer than the bytes left");       // every element takes at least one byte
   }
+  int depth = 0;            // nesting of the value being skipped: a damaged footer must not recurse without bound
   void skip(int type) {
+    struct Nest {
+      int &d;
+      explicit Nest(int &x) : d(x) { if (++d > 64) corrupt("thrift: nesting too deep"); }
+      ~Nest() { --d; }
+    } nest(depth);
     switch (type) {
       case 1: case 2: return;                       // bool inside a field header
       case 3: byte(); return;
@@ -121,9 +128,11 @@ struct Thrift {
       }
       case 11: {
         const uint64_t n = varint();
+        if (n > (uint64_t)(end - p)) corrupt("thrift: map longer than the bytes left");
         if (n) {
           const uint8_t kv = byte();
-          for (uint64_t i = 0; i < n; i++) { skip(kv >> 4); skip(kv & 0x0f); }
+          auto elem = [&](int t) { if (t == 1 || t == 2) byte(); else skip(t); };     // a bool in a container is one byte
+          for (uint64_t i = 0; i < n; i++) { elem(kv >> 4); elem(kv & 0x0f); }
         }
         return;
       }
@@ -304,6 +313,7 @@ void snappy_uncompress(const uint8_t *src, size_t n, std::vector<uint8_t> &out, 
     if (!(b & 0x80)) break;
   }
   if (len != expect) corrupt("snappy: uncompressed size differs from the page header");
+  if (len > 32 * (uint64_t)n + 64) corrupt("snappy: implausible uncompressed size");      // a 3-byte copy yields at most 64 bytes
   out.resize(len);
   uint8_t *o = out.data(), *oend = o + len;
   while (p < end) {
@@ -587,6 +597,9 @@ struct ChunkReader {
       dict.data = body; dict.end = body + h.compressed;
     }
     dict.n = h.num_values;
+    if (dict.n < 0) corrupt("dictionary: negative entry count");
+    if (leaf.type == T_FLBA && (leaf.type_length <= 0 || (int64_t)(dict.end - dict.data) < (int64_t)dict.n * leaf.type_length))
+      corrupt("dictionary: fixed-length entries past the end");
     if (leaf.type == T_BYTE_ARRAY) {
       dict.offs.resize((size_t)dict.n + 1);
       const uint8_t *q = dict.data;
@@ -614,6 +627,7 @@ struct ChunkReader {
       if (h.type == P_DICT) { load_dictionary(h, body); continue; }
       if (h.type == P_INDEX) continue;
       if (h.type != P_DATA && h.type != P_DATA_V2) unsupported("page type " + std::to_string(h.type));
+      if (h.num_values < 0 || (int64_t)h.num_values > values_left) corrupt("page: more values than its column chunk holds");
       pg.num_values = h.num_values;
       pg.encoding = h.encoding;
       pg.skipped = false;
@@ -1114,6 +1128,13 @@ void validate_columns(const FileMeta &m, const ColumnMap &c) {
       if (codec != C_UNCOMPRESSED && codec != C_SNAPPY)
         unsupported("compression codec " + std::to_string(codec) + " (only uncompressed and Snappy pages are decoded)");
     }
+  // value counts against row counts: a flat column has one value slot per row, the list column at least one
+  for (const RowGroupMeta &g : m.row_groups) {
+    if (g.num_rows < 0) corrupt("row group with a negative row count");
+    for (int l : {c.txid, c.height, c.tweak})
+      if (g.cols[(size_t)l].num_values != g.num_rows) corrupt("column " + m.leaves[(size_t)l].path[0] + ": value count differs from the row count");
+    if (g.cols[(size_t)c.outputs].num_values < g.num_rows) corrupt("column " + o.path[0] + ": fewer values than rows");
+  }
 }
 
 struct Match {
@@ -1282,6 +1303,8 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
     return stg::fail(q, CUDASP_ERR_UNSUPPORTED, ("Parquet feature outside the fast path: " + u.what).c_str());
   } catch (const Corrupt &c) {
     return stg::fail(q, CUDASP_ERR_IO, ("malformed Parquet file: " + c.what).c_str());
+  } catch (const std::exception &e) {       // a size read from a damaged footer (length_error, bad_alloc)
+    return stg::fail(q, CUDASP_ERR_IO, (std::string("malformed Parquet file: ") + e.what()).c_str());
   }
   const uint64_t opened_ns = now_ns() - call_t0;
   if (threads <= 0) threads = (int)std::max(1u, std::thread::hardware_concurrency());
@@ -1356,6 +1379,8 @@ extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, in
       rc = CUDASP_ERR_IO; msg = "malformed Parquet file: " + c.what;
     } catch (const std::bad_alloc &) {
       rc = CUDASP_ERR_IO; msg = "out of host memory while decoding a row group";
+    } catch (const std::exception &e) {     // a size read from a damaged page (length_error)
+      rc = CUDASP_ERR_IO; msg = std::string("malformed Parquet file: ") + e.what();
     }
     if (scan) {
       g_clock.ns[5] += stg::column_scan_wait_ns(scan);

@@ -5,6 +5,7 @@ the reference's NULL rules (src/cudasp_extension.cu:195-221) on files written by
 import ctypes as C
 import os
 import subprocess
+import time
 
 import numpy as np
 import pyarrow as pa
@@ -169,6 +170,18 @@ def test_unsupported_and_malformed_files_are_refused(P, tmp_path):
     open(cut, "wb").write(data[: len(data) // 2] + data[-200:])
     assert P([cut])[0] in (ERR_IO, ERR_UNSUPPORTED)
     assert P([])[0] == 0
+    # hand-made footers (found by tests/hostcheck/parquet_fuzz.py): a map of 2^40 one-bit values, which the thrift skipper once
+    # walked element by element, and structs nested 100 000 deep, which it once followed recursively
+    def with_footer(name, footer):
+        f = str(tmp_path / name)
+        open(f, "wb").write(b"PAR1" + footer + len(footer).to_bytes(4, "little") + b"PAR1")
+        return f
+    t0 = time.time()
+    rc, msg = P([with_footer("map.parquet", bytes([0xFB, 0x80, 0x80, 0x80, 0x80, 0x80, 0x20, 0x11, 0x00]))])
+    assert rc == ERR_IO and "map longer" in msg
+    rc, msg = P([with_footer("deep.parquet", bytes([0x1C]) * 100000)])
+    assert rc == ERR_IO and "nesting" in msg
+    assert time.time() - t0 < 5
 
 
 DUCKDB = os.path.join(ROOT, "duckdb-cudasp-extension_b200", "duckdb_ext", "bin", "duckdb")
