@@ -16,6 +16,7 @@
 #include "duckdb/main/extension/extension_loader.hpp"
 #include "duckdb/parallel/task_scheduler.hpp"
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdio>
@@ -905,6 +906,24 @@ static unique_ptr<FunctionData> CudaspParquetBind(ClientContext &context, TableF
 		}
 	} else {
 		throw InvalidInputException("First argument must be a VARCHAR path or a LIST[VARCHAR] of paths");
+	}
+	// glob patterns as in read_parquet('dir/*.parquet'): expanded here, in sorted order; the library maps LOCAL files, so a path
+	// another file system would serve (s3://, http://) is refused by the scan with the read_parquet form to use instead
+	{
+		auto &fs = FileSystem::GetFileSystem(context);
+		vector<string> expanded;
+		for (auto &path : result->paths) {
+			if (!FileSystem::HasGlob(path)) {
+				expanded.push_back(path);
+				continue;
+			}
+			auto found = fs.GlobFiles(path, context, FileGlobOptions::DISALLOW_EMPTY);
+			std::sort(found.begin(), found.end());
+			for (auto &info : found) {
+				expanded.push_back(info.path);
+			}
+		}
+		result->paths = std::move(expanded);
 	}
 	BindKeys(input, *result);
 	auto th = input.named_parameters.find("threads");

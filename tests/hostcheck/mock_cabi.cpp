@@ -227,7 +227,12 @@ int cudasp_release_result(cudasp_query *q, const cudasp_result *r) {
 
 // cudasp_scan_parquet (include/cudasp_parquet.h) needs the real library's page decoders and staging: not in this double
 #include "../../include/cudasp_parquet.h"
-extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *, int, int, cudasp_parquet_result **) {
-  return fail(q, CUDASP_ERR_UNSUPPORTED, "mock: cudasp_scan_parquet needs the GPU build");
+extern "C" int cudasp_scan_parquet(cudasp_query *q, const char *const *paths, int n_paths, int, cudasp_parquet_result **) {
+  std::string m = "mock: cudasp_scan_parquet needs the GPU build; paths:";       // the paths as the extension's bind passed them on
+  for (int i = 0; i < n_paths; i++) {
+    const char *slash = strrchr(paths[i], '/');
+    m += std::string(" ") + (slash ? slash + 1 : paths[i]);
+  }
+  return fail(q, CUDASP_ERR_UNSUPPORTED, m.c_str());
 }
 extern "C" void cudasp_parquet_result_free(cudasp_parquet_result *) {}

@@ -167,3 +167,10 @@ def test_cudasp_scan_parquet_bind_and_refusal(mock, tmp_path):
     assert rc != 0 and "Each label key must be exactly 64 bytes, got 63 bytes" in err
     rc, out, err = run(mock, "SELECT * FROM cudasp_scan_parquet('x.parquet', repeat('\\x01',32)::BLOB, repeat('\\x02',64)::BLOB, []::BLOB[], threads := 2);")
     assert rc != 0 and "use cudasp_scan((SELECT txid, height, tweak_key, outputs FROM read_parquet(...))" in err
+    # glob patterns are expanded at bind time, in sorted order, next to plain paths (the double reports the paths it was handed)
+    for name in ("part_2.parquet", "part_0.parquet", "part_1.parquet", "other.txt"):
+        (tmp_path / name).write_bytes(b"")
+    rc, out, err = run(mock, "SELECT * FROM cudasp_scan_parquet(['%s/part_*.parquet', 'plain.parquet'], %s);" % (tmp_path, KEYS))
+    assert rc != 0 and "paths: part_0.parquet part_1.parquet part_2.parquet plain.parquet" in err
+    rc, out, err = run(mock, "SELECT * FROM cudasp_scan_parquet('%s/none_*.parquet', %s);" % (tmp_path, KEYS))
+    assert rc != 0 and "No files found" in err
