@@ -5,6 +5,7 @@
 // Two staging paths per piece (a piece = up to piece_rows rows, whole K1 waves):
 //   dense   : no NULL keys / lists / children in sight and one key width -> memcpy(keys), rebase(offsets), memcpy(values)
 //   general : row by row with the reference's NULL rules, rows compacted, a row map kept to translate ids back
+// A piece is filled across pushes (record batches, Parquet pages): what a push leaves over stays in an open piece.
 #include <algorithm>
 #include <chrono>
 #include <cstdlib>

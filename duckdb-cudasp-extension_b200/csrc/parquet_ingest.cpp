@@ -1,10 +1,12 @@
-// parquet_ingest.cpp -- include/cudasp_parquet.h: Parquet pages decoded on the host straight into the Arrow ingest.
+// parquet_ingest.cpp -- include/cudasp_parquet.h: Parquet pages decoded on the host straight into the pinned staging slots.
 //
 // Host-only C++ (g++), linked into libcudasp_b200.so.  No reference counterpart (the reference reads tables through DuckDB,
 // README.md:100-110); the Parquet format itself is restated from its public specification (parquet-format: thrift compact
 // protocol footer, PageHeader, data pages V1 / V2, PLAIN / RLE_DICTIONARY encodings, RLE / bit-packed hybrid levels).
-// Layering: this file only DECODES; a decoded row group becomes two Arrow arrays (tweak_key: binary, outputs: list<int64>)
-// handed to cudasp_scan_arrow_columns (arrow_ingest.cpp), which owns the NULL rules, key formats, piece cutting and slots.
+// Layering: this file only DECODES and walks pages; staging belongs to arrow_ingest.cpp (NULL rules, key formats, piece cutting,
+// slots), reached through staging_internal.hpp's ColumnScan: one scan per decoder thread, fed page by page with either a view of
+// the keys where they lie in the file mapping (column_scan_push_keys) or Arrow arrays of a decoded page (column_scan_push), and
+// the row group's outputs as a list<int64> array sliced per page.
 #include <fcntl.h>
 #include <sys/mman.h>
 #include <sys/stat.h>

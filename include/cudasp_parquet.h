@@ -5,9 +5,11 @@
  * AccumulateInput (README.md:100-110, src/cudasp_extension.cu:154-224), and its README names that table scan as the scaling
  * limit (README.md:136-140).  Measured here on 8 B200: DuckDB's own decode of the four columns takes as long as the whole
  * scan from a DuckDB table -- so this entry decodes the pages itself (csrc/parquet_ingest.cpp: thrift footer,
- * data pages V1/V2, PLAIN and dictionary encodings, RLE/bit-packed levels) with one thread per row group in flight, hands each
- * row group to the Arrow ingest as two arrays (the same NULL rules, key formats, piece cutting and slot recycling as
- * cudasp_arrow.h), and keeps txid / height only to return them for the rows that matched.
+ * data pages V1/V2, PLAIN and dictionary encodings, RLE/bit-packed levels) with one thread per row group in flight.  A page of
+ * plain 64- or 33-byte keys without NULLs is staged into the pinned slots from where it lies in the file mapping; any other
+ * page is decoded first and takes the Arrow ingest's path (the same NULL rules, key formats, piece cutting and slot recycling
+ * as cudasp_arrow.h).  txid and height are read only for the rows that matched.  DESIGN.md 9.7: 100 M rows on 8 B200 in
+ * 0.300 s against 0.416 s through read_parquet.
  *
  * Deliberately a SUBSET of Parquet: uncompressed or Snappy-compressed pages; the four columns
  *     txid BYTE_ARRAY | FIXED_LEN_BYTE_ARRAY, height INT32, tweak_key BYTE_ARRAY | FIXED_LEN_BYTE_ARRAY, outputs LIST<INT64>
