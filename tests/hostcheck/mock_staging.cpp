@@ -4,6 +4,9 @@
 // equals the int64 read little-endian from key bytes [1, 9).  TEST INFRASTRUCTURE ONLY; never linked into the product.
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -24,6 +27,8 @@ struct cudasp_query {
   uint64_t cap_outputs = 0;
   std::vector<MockSlot> slots;
   std::string err;
+  std::condition_variable freed;
+  std::mutex mu;               // the slot table and the counters: several front-end threads may share one query (Parquet decoder threads)
   uint64_t n_submits = 0, rows_staged = 0, n_submits_sec1 = 0, outputs_staged = 0, max_in_flight = 0, n_reserve = 0;
 };
 
@@ -39,24 +44,31 @@ static void view(Staging *v, MockSlot *s, cudasp_query *q) {
   v->cap_outputs = s->outputs.size();
 }
 int acquire(cudasp_query *q, Staging *v, bool block) {
-  uint64_t busy = 0;
-  for (MockSlot &s : q->slots) busy += s.busy;
-  for (MockSlot &s : q->slots) {
-    if (!s.busy) {
-      s.busy = true;
-      s.submitted = false;
-      memset(s.tweaks.data(), 0xEE, s.tweaks.size());        // stale data must never be read
-      if (busy + 1 > q->max_in_flight) q->max_in_flight = busy + 1;
-      view(v, &s, q);
-      return 1;
+  std::unique_lock<std::mutex> lk(q->mu);
+  for (;;) {
+    uint64_t busy = 0;
+    for (MockSlot &s : q->slots) busy += s.busy;
+    for (MockSlot &s : q->slots) {
+      if (!s.busy) {
+        s.busy = true;
+        s.submitted = false;
+        memset(s.tweaks.data(), 0xEE, s.tweaks.size());        // stale data must never be read
+        if (busy + 1 > q->max_in_flight) q->max_in_flight = busy + 1;
+        view(v, &s, q);
+        return 1;
+      }
+    }
+    if (!block) return 0;
+    // another front-end thread may release a slot; a lone caller that blocks with every slot its own would wait for ever
+    if (q->freed.wait_for(lk, std::chrono::seconds(2)) == std::cv_status::timeout) {
+      lk.unlock();
+      return fail(q, CUDASP_ERR_STATE, "mock: blocking acquire with every slot busy would deadlock");
     }
   }
-  if (block) return fail(q, CUDASP_ERR_STATE, "mock: blocking acquire with every slot busy would deadlock");
-  return 0;
 }
 int reserve_outputs(cudasp_query *q, Staging *v, uint64_t n) {
   MockSlot *s = static_cast<MockSlot *>(v->slot);
-  q->n_reserve++;
+  { std::lock_guard<std::mutex> lk(q->mu); q->n_reserve++; }
   if (n > s->outputs.size()) s->outputs.resize(n + n / 4);
   view(v, s, q);
   return 0;
@@ -80,10 +92,13 @@ int submit(cudasp_query *q, Staging *v, uint32_t rows, uint64_t n_outputs, int k
   s->rows = rows;
   s->fmt = key_format;
   s->submitted = true;
-  q->n_submits++;
-  q->rows_staged += rows;
-  q->outputs_staged += n_outputs;
-  q->n_submits_sec1 += key_format == CUDASP_KEYS_SEC1_33;
+  {
+    std::lock_guard<std::mutex> lk(q->mu);
+    q->n_submits++;
+    q->rows_staged += rows;
+    q->outputs_staged += n_outputs;
+    q->n_submits_sec1 += key_format == CUDASP_KEYS_SEC1_33;
+  }
   view(v, s, q);
   return 0;
 }
@@ -94,16 +109,21 @@ int finish(cudasp_query *q, Staging *v, uint32_t *n) {
   v->ids = s->ids.data();
   return 0;
 }
-void release(cudasp_query *, Staging *v) {
-  if (v->slot) static_cast<MockSlot *>(v->slot)->busy = false;
+void release(cudasp_query *q, Staging *v) {
+  if (v->slot) {
+    std::lock_guard<std::mutex> lk(q->mu);
+    static_cast<MockSlot *>(v->slot)->busy = false;
+    q->freed.notify_all();
+  }
   v->slot = nullptr;
 }
 uint32_t piece_rows(cudasp_query *q) { return q->piece; }
 int device_count(cudasp_query *) { return 1; }
 int fail(cudasp_query *q, int code, const char *msg) {
-  static std::string last;
-  last = msg;
-  if (q) q->err = msg;
+  if (q) {
+    std::lock_guard<std::mutex> lk(q->mu);
+    q->err = msg;
+  }
   return code;
 }
 }  // namespace staging

@@ -41,12 +41,12 @@ def P():
     L.cudasp_scan_parquet.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int, C.c_int, C.POINTER(C.POINTER(Result))]
     L.cudasp_parquet_result_free.argtypes = [C.POINTER(Result)]
 
-    def scan(paths, piece=97, cap_rows=128, cap_outputs=1024, stats=None):
-        q = L.mock_query_create(piece, cap_rows, cap_outputs, 3)
+    def scan(paths, piece=97, cap_rows=128, cap_outputs=1024, stats=None, threads=1, slots=3):
+        q = L.mock_query_create(piece, cap_rows, cap_outputs, slots)
         try:
             arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
             out = C.POINTER(Result)()
-            rc = L.cudasp_scan_parquet(q, arr, len(paths), 1, C.byref(out))      # the staging double is single-threaded
+            rc = L.cudasp_scan_parquet(q, arr, len(paths), threads, C.byref(out))
             if rc:
                 return rc, (L.cudasp_last_error(q) or b"").decode()
             r = out.contents
@@ -255,3 +255,21 @@ def test_dense_pages_staged_where_they_lie(P, tmp_path, key_type, settings):
     assert rc == 0, res
     assert res[0] == n and st["rows"] == n
     assert [(g[1], g[2], g[3], g[4]) for g in res[1]] == [(int(i), txid[i].tobytes(), int(height[i]), keys[i].tobytes()) for i in hit]
+
+
+@pytest.mark.parametrize("threads,slots", [(4, 6), (8, 3), (3, 1)])
+def test_decoder_threads_share_one_query(P, tmp_path, threads, slots):
+    """Several decoder threads, each with its own scan over the row groups it takes, on one query: the result is the
+    single-threaded one (file order, then row order) whatever the interleaving -- also with fewer slots than threads, where a
+    thread holding an open piece makes the others wait."""
+    rows, expect = make_rows(6000, 321, p_null=0.03, key_sizes=(64, 64, 33))
+    paths = []
+    for i, st in enumerate((0, 4)):
+        path = str(tmp_path / ("f%d.parquet" % i))
+        pq.write_table(table_of(rows), path, row_group_size=250, **WRITER_SETTINGS[st])
+        paths.append(path)
+    st = {}
+    rc, res = P(paths, piece=128, cap_rows=128, cap_outputs=4096, stats=st, threads=threads, slots=slots)
+    assert rc == 0, res
+    assert res[0] == 12000
+    assert [(g[0],) + g[1:] for g in res[1]] == [(0,) + e for e in expect] + [(1,) + e for e in expect]
