@@ -256,3 +256,35 @@ def test_open_piece_is_cut_when_outputs_do_not_fit(A):
     assert st["rows"] == n and st["outputs"] == 10 * n and st["reserves"] == 0
     # 128 outputs hold 12 rows; the dense path does not split a batch of 8 to fill the last 4: 8 rows a piece
     assert st["submits"] == 5
+
+
+def test_open_pieces_random_streams(A):
+    """Randomised streams (seeded): batch sizes from 0 to a few pieces, piece sizes, output capacities small enough to cut pieces
+    early and to force an empty piece's staging to grow, mixed key lengths (format switches inside and between batches), NULL
+    keys / lists / children -- the match set is always the closed form, every staged row is staged once, no slot leaks."""
+    rng = np.random.default_rng(20251105)
+    for case in range(60):
+        piece = int(rng.choice([16, 64, 128]))
+        cap_outputs = int(rng.choice([8, 40, 400, 4096]))
+        slots = int(rng.integers(1, 4))
+        n_batches = int(rng.integers(1, 9))
+        mixed = rng.random() < 0.4
+        nulls = rng.random() < 0.5
+        parts, expect, base, staged = [], [], 0, 0
+        for b in range(n_batches):
+            n = int(rng.choice([0, 1, 5, int(rng.integers(1, 3 * piece + 5))]))
+            keys, lists, e = make_rows(n, 1000 * case + b, p_match=0.3, key_sizes=(64, 33) if mixed else (64,),
+                                       p_null_key=0.1 if nulls else 0.0, p_null_list=0.1 if nulls else 0.0,
+                                       p_null_child=0.15 if nulls else 0.0, p_bad_len=0.05 if mixed else 0.0)
+            parts.append(batch_of(keys, lists))
+            expect.extend((e + base).tolist())
+            staged += sum(k is not None and len(k) in (33, 64) for k in keys)
+            base += n
+        with A.query(piece=piece, cap_rows=piece, cap_outputs=cap_outputs, slots=slots) as q:
+            reader = pa.RecordBatchReader.from_batches(parts[0].schema, parts)
+            ids, seen = A.arrow.scan_stream(q.h, reader, _lib=A.lib)
+            st = q.stats()
+        assert ids.tolist() == expect and seen == base, (case, piece, cap_outputs, slots)
+        assert st["rows"] == staged, (case, st, staged)
+        if not mixed and not nulls and cap_outputs == 4096:
+            assert st["submits"] == -(-staged // piece), (case, st, staged, piece)     # whole pieces across batches
